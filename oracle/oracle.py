@@ -1,0 +1,206 @@
+"""ctypes/numpy face of the CPU oracle (oracle/ntt_oracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product package never
+imports this module.  Parity status: see the header of ntt_oracle.c
+("parity unpinned" at bit level against SEAL/Phantom, whose sources are absent).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+U64P = C.POINTER(C.c_uint64)
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    src = os.path.join(_HERE, "ntt_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build())
+        u64, i32 = C.c_uint64, C.c_int
+        for name, res, args in [
+            ("orc_mulmod", u64, [u64, u64, u64]),
+            ("orc_powmod", u64, [u64, u64, u64]),
+            ("orc_invmod", u64, [u64, u64]),
+            ("orc_shoup", u64, [u64, u64]),
+            ("orc_barrett_ratio", None, [u64, U64P]),
+            ("orc_barrett_reduce128", u64, [u64, u64, u64, U64P]),
+            ("orc_is_prime", i32, [u64]),
+            ("orc_primes_create", i32, [u64, C.POINTER(i32), i32, U64P]),
+            ("orc_find_ntt_prime", u64, [u64, i32]),
+            ("orc_find_primitive_root_relia", u64, [u64]),
+            ("orc_min_primitive_root", u64, [u64, u64]),
+            ("orc_bitrev", u64, [u64, i32]),
+            ("orc_ntt_tables", None, [i32, u64, u64, U64P, U64P, U64P, U64P]),
+            ("orc_ntt_forward_def", None, [U64P, U64P, i32, u64, u64]),
+            ("orc_ntt_forward_simple", None, [U64P, i32, u64, U64P]),
+            ("orc_ntt_inverse_simple", None, [U64P, i32, u64, U64P]),
+            ("orc_ntt_forward_harvey", None, [U64P, i32, u64, U64P, U64P]),
+            ("orc_ntt_inverse_harvey", None, [U64P, i32, u64, U64P, U64P]),
+            ("orc_ntt_forward_batch", None, [U64P, i32, i32, U64P, U64P, U64P]),
+            ("orc_ntt_inverse_batch", None, [U64P, i32, i32, U64P, U64P, U64P]),
+            ("orc_negacyclic_mul_naive", None, [U64P, U64P, U64P, u64, u64]),
+            ("orc_pmult_accum", None, [U64P, U64P, U64P, i32, i32, i32, u64, U64P]),
+            ("orc_bconv_hps", None, [U64P, U64P, i32, i32, u64, U64P, U64P]),
+            ("orc_bconv_proto", None, [U64P, U64P, i32, i32, u64, U64P, U64P]),
+            ("orc_root_of_unity", u64, [u64, u64, u64]),
+            ("orc_cyclic_ntt_direct", None, [U64P, U64P, u64, u64, u64]),
+            ("orc_four_step_cyclic", i32, [U64P, U64P, u64, u64, u64, U64P, U64P]),
+            ("orc_protection_check_blockdiag", i32, [U64P, U64P, u64, u64, u64, u64, U64P, U64P]),
+        ]:
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    assert a.dtype == np.uint64 and a.flags.c_contiguous
+    return a.ctypes.data_as(U64P)
+
+
+def primes_create(N, bits):
+    bits = list(bits)
+    arr = (C.c_int * len(bits))(*bits)
+    out = np.zeros(len(bits), dtype=np.uint64)
+    rc = lib().orc_primes_create(N, arr, len(bits), _p(out))
+    if rc:
+        raise ValueError("primes_create failed rc=%d" % rc)
+    return [int(x) for x in out]
+
+
+def min_root(N, q):
+    return int(lib().orc_min_primitive_root(2 * N, q))
+
+
+class Tables:
+    """Per-modulus tables in the layout ntt_test.cu:60-68 uploads."""
+
+    def __init__(self, logn, q, psi=None):
+        self.logn, self.q = logn, int(q)
+        self.N = 1 << logn
+        self.psi = int(psi) if psi else min_root(self.N, self.q)
+        self.rp = np.zeros(self.N, dtype=np.uint64)
+        self.rps = np.zeros(self.N, dtype=np.uint64)
+        self.irp = np.zeros(self.N, dtype=np.uint64)
+        self.irps = np.zeros(self.N, dtype=np.uint64)
+        lib().orc_ntt_tables(logn, self.q, self.psi, _p(self.rp), _p(self.rps), _p(self.irp), _p(self.irps))
+
+
+def ntt_forward(a, tab, kind="harvey"):
+    a = np.ascontiguousarray(a, dtype=np.uint64).copy()
+    if kind == "harvey":
+        lib().orc_ntt_forward_harvey(_p(a), tab.logn, tab.q, _p(tab.rp), _p(tab.rps))
+    elif kind == "simple":
+        lib().orc_ntt_forward_simple(_p(a), tab.logn, tab.q, _p(tab.rp))
+    else:
+        out = np.zeros_like(a)
+        lib().orc_ntt_forward_def(_p(a), _p(out), tab.logn, tab.q, tab.psi)
+        a = out
+    return a
+
+
+def ntt_inverse(a, tab, kind="harvey"):
+    a = np.ascontiguousarray(a, dtype=np.uint64).copy()
+    if kind == "harvey":
+        lib().orc_ntt_inverse_harvey(_p(a), tab.logn, tab.q, _p(tab.irp), _p(tab.irps))
+    else:
+        lib().orc_ntt_inverse_simple(_p(a), tab.logn, tab.q, _p(tab.irp))
+    return a
+
+
+def ntt_forward_batch(a, tabs, inplace=False):
+    """a: [L][N]; limb l uses tabs[l]."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    if not inplace:
+        a = a.copy()
+    L = len(tabs)
+    q = np.array([t.q for t in tabs], dtype=np.uint64)
+    rp = np.stack([t.rp for t in tabs]); rps = np.stack([t.rps for t in tabs])
+    lib().orc_ntt_forward_batch(_p(a), tabs[0].logn, L, _p(q), _p(rp), _p(rps))
+    return a
+
+
+def ntt_inverse_batch(a, tabs, inplace=False):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    if not inplace:
+        a = a.copy()
+    L = len(tabs)
+    q = np.array([t.q for t in tabs], dtype=np.uint64)
+    irp = np.stack([t.irp for t in tabs]); irps = np.stack([t.irps for t in tabs])
+    lib().orc_ntt_inverse_batch(_p(a), tabs[0].logn, L, _p(q), _p(irp), _p(irps))
+    return a
+
+
+def pmult_accum(ct, pt, q):
+    """ct [T][P][L][N], pt [T][L][N] -> out [P][L][N]."""
+    ct = np.ascontiguousarray(ct, dtype=np.uint64); pt = np.ascontiguousarray(pt, dtype=np.uint64)
+    T, P, L, N = ct.shape
+    out = np.zeros((P, L, N), dtype=np.uint64)
+    qa = np.array(q, dtype=np.uint64)
+    lib().orc_pmult_accum(_p(ct), _p(pt), _p(out), T, P, L, N, _p(qa))
+    return out
+
+
+def bconv_hps(x, p, qo):
+    """x [m][N] mod p_j -> [K][N] mod qo_k (HPS fast base conversion)."""
+    x = np.ascontiguousarray(x, dtype=np.uint64)
+    m, N = x.shape
+    out = np.zeros((len(qo), N), dtype=np.uint64)
+    pa = np.array(p, dtype=np.uint64); qa = np.array(qo, dtype=np.uint64)
+    lib().orc_bconv_hps(_p(x), _p(out), m, len(qo), N, _p(pa), _p(qa))
+    return out
+
+
+def bconv_proto(x, p, qo):
+    """rfhe_framewk/src/baseConv.py:10-40 bConv: returns result[i][k]."""
+    x = np.ascontiguousarray(x, dtype=np.uint64)
+    m, N = x.shape
+    out = np.zeros((N, len(qo)), dtype=np.uint64)
+    pa = np.array(p, dtype=np.uint64); qa = np.array(qo, dtype=np.uint64)
+    lib().orc_bconv_proto(_p(x), _p(out), m, len(qo), N, _p(pa), _p(qa))
+    return out
+
+
+def cyclic_ntt_direct(a, N, mod, g):
+    a = np.ascontiguousarray(a, dtype=np.uint64); y = np.zeros(N, dtype=np.uint64)
+    lib().orc_cyclic_ntt_direct(_p(a), _p(y), N, mod, g)
+    return y
+
+
+def four_step_cyclic(a, N, mod, g):
+    """four_step_ntt_prot.py:71-109; returns (y, B after step 1, C after twiddle)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    y = np.zeros(N, dtype=np.uint64); B = np.zeros(N, dtype=np.uint64); Cc = np.zeros(N, dtype=np.uint64)
+    rc = lib().orc_four_step_cyclic(_p(a), _p(y), N, mod, g, _p(B), _p(Cc))
+    if rc:
+        raise ValueError("N must be a perfect square")
+    return y, B, Cc
+
+
+def splitmix64(x):
+    x = (x + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+    z = x
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return z ^ (z >> 31)
+
+
+def uniform_limbs(moduli, N, seed=20250606):
+    """[L][N] with limb l i.i.d. uniform on [0,q_l) (numpy Generator, seeded)."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((len(moduli), N), dtype=np.uint64)
+    for l, q in enumerate(moduli):
+        out[l] = rng.integers(0, int(q), size=N, dtype=np.uint64)
+    return out
