@@ -1,0 +1,256 @@
+#!/usr/bin/env python
+"""Headline benchmark: NTT limb-transforms/s at N=2^16, 60-bit RNS (BASELINE.json).
+
+Workload (config C2, reliability_test/ntt_test.cu shape scaled to N=2^16, L=36):
+a batch of NPOLY polynomials x 36 limbs, forward NTT of the whole batch then
+inverse NTT of the whole batch, in place.  One step = 2*NPOLY*36 limb-transforms.
+The batch (144 MiB at NPOLY=8) is larger than the 126 MB L2, so every transform
+reads its input from HBM ("inputs larger than L2").
+
+  value  : device-resident throughput, CUDA events, max over ranks
+  e2e    : same metric through b200fhe_nwt_{forward,backward}_host with pinned
+           HOST buffers (H2D + kernels + D2H inside the timed region)
+  --impl reference : the CPU oracle (restated SEAL Harvey NTT, all host cores)
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LOG_N, L, BITS, NPOLY = 16, 36, 60, 8
+N = 1 << LOG_N
+SEED = 20250606
+MIB = 1 << 20
+ALGO_BYTES_PER_LIMB_TRANSFORM = 16 * N     # read once + write once
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_reference(steps, warmup, sample_polys=1):
+    """Oracle (restated SEAL Harvey NTT) on all host cores: fwd+inv of
+    sample_polys x 36 limbs per step."""
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    moduli = O.primes_create(N, [BITS] * L)
+    tabs = [O.Tables(LOG_N, q) for q in moduli]
+    a = np.stack([O.uniform_limbs(moduli, N, seed=SEED + i) for i in range(sample_polys)])
+    ref = a.copy()
+    def step():
+        for i in range(sample_polys):
+            O.ntt_forward_batch(a[i], tabs, inplace=True)
+        for i in range(sample_polys):
+            O.ntt_inverse_batch(a[i], tabs, inplace=True)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    assert np.array_equal(a, ref), "oracle round trip failed"
+    per_step = 2 * sample_polys * L
+    return per_step * steps / dt, dt / steps * 1e3, cores, "%d poly x %d limbs fwd+inv per step, %d steps" % (sample_polys, L, steps)
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, dev):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(dev), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        out = self.p.communicate()[0]
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--npoly", type=int, default=NPOLY)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    config = {"workload": "C2: N=2^16, L=36 x 60-bit RNS limbs, batch of %d polys per GPU, forward NTT of the batch then inverse NTT of the batch, in place" % args.npoly,
+              "log_n": LOG_N, "limbs": L, "prime_bits": BITS, "polys_per_gpu": args.npoly,
+              "cache": "inputs larger than L2 (%d MiB per GPU vs 126 MB L2)" % (args.npoly * L * N * 8 // MIB),
+              "sharding": "limb/ciphertext-sharded, no collective", "seed": SEED}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        steps = max(1, min(args.steps, 20)); warm = max(1, min(args.warmup, 3))
+        v, ms, cores, sample = cpu_reference(steps, warm)
+        print(json.dumps({"impl": "reference", "metric": "NTT limb-transforms/s", "value": v, "unit": "limb-transforms/s",
+                          "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": v, "unit": "limb-transforms/s", "cores": cores, "kind": "port", "sample": sample},
+                          "e2e": {"value": v, "unit": "limb-transforms/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    import fhe_reliability_gpu_b200 as pkg
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = pkg.lib()
+    moduli = pkg.primes_create(N, [BITS] * L)
+    ctx = pkg.Context(LOG_N, moduli, device=local)
+    npoly = args.npoly
+    words = npoly * L * N
+    # synthetic input: uniform residues, seeded per rank (disjoint data per GPU)
+    rng = np.random.default_rng(SEED + rank)
+    h = torch.empty(words, dtype=torch.int64).pin_memory()
+    hv = h.numpy().view(np.uint64).reshape(npoly, L, N)
+    for l, q in enumerate(moduli):
+        hv[:, l, :] = rng.integers(0, q, size=(npoly, N), dtype=np.uint64)
+    ref0 = hv[0].copy()
+    d = h.to("cuda", non_blocking=False)
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+    dp = d.data_ptr()
+
+    def step():
+        pkg.binding.check(lib.b200fhe_nwt_forward(ctx._h, dp, npoly, L, 0, sp))
+        pkg.binding.check(lib.b200fhe_nwt_backward(ctx._h, dp, npoly, L, 0, sp))
+
+    # correctness gate before timing: forward of poly 0 vs oracle, then round trip
+    from oracle import oracle as O
+    if rank == 0:
+        pkg.binding.check(lib.b200fhe_nwt_forward(ctx._h, dp, 1, L, 0, sp))
+        got = d[:L * N].cpu().numpy().view(np.uint64).reshape(L, N)
+        tabs3 = {l: O.Tables(LOG_N, moduli[l]) for l in (0, 35)}
+        for l, t in tabs3.items():
+            assert np.array_equal(got[l], O.ntt_forward(ref0[l], t)), "GPU forward != oracle (limb %d)" % l
+        pkg.binding.check(lib.b200fhe_nwt_backward(ctx._h, dp, 1, L, 0, sp))
+        assert np.array_equal(d[:L * N].cpu().numpy().view(np.uint64).reshape(L, N), ref0), "round trip failed"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = lib.b200fhe_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    launches = int(lib.b200fhe_launch_count() - l0)
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    per_step_units = 2 * npoly * L * world
+    value = per_step_units * args.steps / (ms_total * 1e-3)
+    assert np.array_equal(d[:L * N].cpu().numpy().view(np.uint64).reshape(L, N), ref0), "data corrupted by timed loop"
+
+    # per-kernel timings (each of the four kernels over the whole batch), CUDA events on the launch stream
+    kern = {}
+    reps = 5
+    for inv, ps, name in [(0, 1, "k_fwd_col"), (0, 2, "k_fwd_row"), (1, 1, "k_inv_row"), (1, 2, "k_inv_col")]:
+        for _ in range(2):
+            lib.b200fhe_debug_nwt_pass(ctx._h, dp, npoly, L, 0, inv, ps, sp)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(stream)
+        for _ in range(reps):
+            lib.b200fhe_debug_nwt_pass(ctx._h, dp, npoly, L, 0, inv, ps, sp)
+        a1.record(stream)
+        torch.cuda.synchronize()
+        kern[name] = a0.elapsed_time(a1) / reps
+    peak, peak_src = peaks()
+    dom = max(kern, key=kern.get)
+    # one pass kernel = half of a limb-transform's 16 B/coeff (the pair shares the 1 MiB)
+    algo_bytes_launch = npoly * L * ALGO_BYTES_PER_LIMB_TRANSFORM / 2
+    ach = algo_bytes_launch / (kern[dom] * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes_launch,
+            "kernel_ms": kern, "note": "standalone whole-batch pass: intermediate not L2-resident (worst case); "
+            "transform_frac = limb-transforms/s x 1 MiB / peak",
+            "transform_frac": value / world * ALGO_BYTES_PER_LIMB_TRANSFORM / 1e9 / peak}
+
+    # e2e: host buffers through the C ABI (H2D + kernels + D2H per call)
+    hp = hv.ctypes.data_as(C.POINTER(C.c_uint64))
+    def e2e_step():
+        pkg.binding.check(lib.b200fhe_nwt_forward_host(ctx._h, hp, npoly, L, 0))
+        pkg.binding.check(lib.b200fhe_nwt_backward_host(ctx._h, hp, npoly, L, 0))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    e2e_val = per_step_units * e2e_steps / float(tt.item())
+    assert np.array_equal(hv[0], ref0), "e2e round trip failed"
+    bytes_dir = 2 * npoly * L * N * 8      # fwd call + inv call, each copies the batch in and out
+
+    if rank == 0:
+        out = {"metric": "NTT limb-transforms/s", "value": value, "unit": "limb-transforms/s", "n_gpus": world,
+               "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+               "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+               "config": config, "clocks": clocks, "gpu_launches": launches,
+               "e2e": {"value": e2e_val, "unit": "limb-transforms/s", "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir,
+                       "steps": e2e_steps, "timer": "host perf_counter around synchronous C-ABI calls, max over ranks"},
+               "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            v, ms, cores, sample = cpu_reference(10, 1)
+            out["cpu_baseline"] = {"value": v, "unit": "limb-transforms/s", "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

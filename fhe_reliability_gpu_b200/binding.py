@@ -1,0 +1,137 @@
+"""ctypes binding of lib/libb200fhe.so (include/b200fhe.h).
+
+This is the host-side mirror the Python prototypes/scripts call.  There is no
+CPU fallback: if the shared library is missing, or no CUDA device is usable,
+every compute entry raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libb200fhe.so")
+_lib = None
+
+u64, i32, sz, vp = C.c_uint64, C.c_int, C.c_size_t, C.c_void_p
+U64P = C.POINTER(C.c_uint64)
+
+# name -> (restype, argtypes); MUST list every symbol include/b200fhe.h declares
+SIGNATURES = {
+    "b200fhe_version": (i32, []),
+    "b200fhe_last_error": (C.c_char_p, []),
+    "b200fhe_primes_create": (i32, [u64, C.POINTER(i32), i32, U64P]),
+    "b200fhe_min_primitive_root": (i32, [u64, u64, U64P]),
+    "b200fhe_host_tables": (i32, [i32, u64, U64P, U64P, U64P, U64P, U64P, U64P]),
+    "b200fhe_const_ratio": (i32, [u64, U64P]),
+    "b200fhe_ctx_create": (i32, [i32, U64P, i32, i32, C.POINTER(vp)]),
+    "b200fhe_ctx_create_empty": (i32, [i32, i32, i32, C.POINTER(vp)]),
+    "b200fhe_ctx_set_tables": (i32, [vp, i32, u64, U64P, U64P, U64P, U64P, u64, u64, vp]),
+    "b200fhe_ctx_destroy": (i32, [vp]),
+    "b200fhe_ctx_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "b200fhe_ctx_moduli": (i32, [vp, U64P]),
+    "b200fhe_nwt_forward": (i32, [vp, vp, sz, sz, sz, vp]),
+    "b200fhe_nwt_backward": (i32, [vp, vp, sz, sz, sz, vp]),
+    "b200fhe_nwt_forward_host": (i32, [vp, U64P, sz, sz, sz]),
+    "b200fhe_nwt_backward_host": (i32, [vp, U64P, sz, sz, sz]),
+    "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
+    "b200fhe_host_alloc": (i32, [C.POINTER(vp), sz]),
+    "b200fhe_host_free": (i32, [vp]),
+    "b200fhe_debug_nwt_pass": (i32, [vp, vp, sz, sz, sz, i32, i32, vp]),
+    "b200fhe_launch_count": (C.c_ulonglong, []),
+}
+
+
+class B200FHEError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B200FHEError(
+                "%s not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(no CPU fallback exists)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise B200FHEError("b200fhe error %d: %s" % (rc, lib().b200fhe_last_error().decode()))
+
+
+def _p(a):
+    assert a.dtype == np.uint64 and a.flags.c_contiguous
+    return a.ctypes.data_as(U64P)
+
+
+def primes_create(N, bits):
+    bits = list(bits)
+    out = np.zeros(len(bits), dtype=np.uint64)
+    check(lib().b200fhe_primes_create(N, (i32 * len(bits))(*bits), len(bits), _p(out)))
+    return [int(x) for x in out]
+
+
+def min_primitive_root(N, q):
+    r = u64(0)
+    check(lib().b200fhe_min_primitive_root(N, q, C.byref(r)))
+    return int(r.value)
+
+
+def host_tables(log_n, q):
+    N = 1 << log_n
+    arrs = [np.zeros(N, dtype=np.uint64) for _ in range(4)]
+    ni, nis = u64(0), u64(0)
+    check(lib().b200fhe_host_tables(log_n, q, *[_p(a) for a in arrs], C.byref(ni), C.byref(nis)))
+    return arrs + [int(ni.value), int(nis.value)]
+
+
+class Context:
+    """Moduli + tables resident on one GPU (b200fhe_ctx)."""
+
+    def __init__(self, log_n, moduli, device=0):
+        self.log_n, self.N = log_n, 1 << log_n
+        self.moduli = [int(q) for q in moduli]
+        self.L = len(self.moduli)
+        self.device = device
+        arr = np.array(self.moduli, dtype=np.uint64)
+        h = vp()
+        check(lib().b200fhe_ctx_create(log_n, _p(arr), self.L, device, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200fhe_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # ---- device-pointer entry points (ptr: int device address, stream: int cudaStream_t)
+    def nwt_forward(self, ptr, n_poly, L=None, start_mod=0, stream=0):
+        check(lib().b200fhe_nwt_forward(self._h, ptr, n_poly, self.L if L is None else L, start_mod, stream))
+
+    def nwt_backward(self, ptr, n_poly, L=None, start_mod=0, stream=0):
+        check(lib().b200fhe_nwt_backward(self._h, ptr, n_poly, self.L if L is None else L, start_mod, stream))
+
+    # ---- host-buffer entry points (numpy uint64 [n_poly][L][N], in place)
+    def _host(self, fn, a, L, start_mod):
+        L = self.L if L is None else L
+        assert a.dtype == np.uint64 and a.flags.c_contiguous and a.size % (L * self.N) == 0
+        check(fn(self._h, _p(a), a.size // (L * self.N), L, start_mod))
+        return a
+
+    def nwt_forward_host(self, a, L=None, start_mod=0):
+        return self._host(lib().b200fhe_nwt_forward_host, a, L, start_mod)
+
+    def nwt_backward_host(self, a, L=None, start_mod=0):
+        return self._host(lib().b200fhe_nwt_backward_host, a, L, start_mod)
+
+
+def flip_bit(ptr, idx, bit, stream=0):
+    check(lib().b200fhe_flip_bit(ptr, idx, bit, stream))

@@ -1,0 +1,340 @@
+// C ABI (include/b200fhe.h): context management and the NTT entry points.
+#include "../../include/b200fhe.h"
+#include "ctx.hpp"
+#include "numth.hpp"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+using namespace b200;
+
+static thread_local char g_err[512] = "";
+
+int b200_set_err(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return b200_set_err(B200FHE_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                __FILE__, __LINE__);                                               \
+    } while (0)
+
+extern "C" int b200fhe_version(void) { return 100; }
+extern "C" const char* b200fhe_last_error(void) { return g_err; }
+
+extern "C" int b200fhe_primes_create(uint64_t N, const int* bits, int n, uint64_t* out) {
+    if (!bits || !out || n < 0 || N < 2 || (N & (N - 1))) return b200_set_err(B200FHE_EINVAL, "primes_create: bad args");
+    if (!nt::primes_create(N, bits, n, out)) return b200_set_err(B200FHE_EINVAL, "primes_create: not enough primes");
+    return 0;
+}
+extern "C" int b200fhe_min_primitive_root(uint64_t N, uint64_t q, uint64_t* psi) {
+    if (!psi) return b200_set_err(B200FHE_EINVAL, "null psi");
+    uint64_t r = nt::min_primitive_root(2 * N, q);
+    if (!r) return b200_set_err(B200FHE_EINVAL, "no primitive 2N-th root: q=%llu N=%llu", (unsigned long long)q, (unsigned long long)N);
+    *psi = r;
+    return 0;
+}
+extern "C" int b200fhe_host_tables(int log_n, uint64_t q, uint64_t* rp, uint64_t* rps, uint64_t* irp, uint64_t* irps,
+                                   uint64_t* n_inv, uint64_t* n_inv_shoup) {
+    if (log_n < 1 || log_n > 20) return b200_set_err(B200FHE_EINVAL, "log_n out of range");
+    uint64_t psi = nt::min_primitive_root((uint64_t)2 << log_n, q);
+    if (!psi) return b200_set_err(B200FHE_EINVAL, "modulus %llu has no primitive 2N-th root", (unsigned long long)q);
+    nt::tables(log_n, q, psi, rp, rps, irp, irps);
+    uint64_t ni = nt::invmod(((uint64_t)1 << log_n) % q, q);
+    if (n_inv) *n_inv = ni;
+    if (n_inv_shoup) *n_inv_shoup = nt::shoup(ni, q);
+    return 0;
+}
+extern "C" int b200fhe_const_ratio(uint64_t q, uint64_t ratio[2]) {
+    if (q < 2 || !ratio) return b200_set_err(B200FHE_EINVAL, "bad modulus");
+    nt::const_ratio(q, ratio);
+    return 0;
+}
+
+// ---------------------------------------------------------------- context
+static B200Mod make_mod(uint64_t q, int log_n, uint64_t itw1, uint64_t n_inv) {
+    B200Mod m;
+    memset(&m, 0, sizeof(m));
+    m.q = q;
+    m.bmu = ~(uint64_t)0 / q;
+    m.ninv = n_inv;
+    m.ninv_s = nt::shoup(n_inv, q);
+    m.iw1n = nt::mulmod(itw1, n_inv, q);
+    m.iw1n_s = nt::shoup(m.iw1n, q);
+    uint64_t r[2];
+    nt::const_ratio(q, r);
+    m.ratio0 = r[0];
+    m.ratio1 = r[1];
+    m.bits = nt::bitlen(q);
+    m.big = m.bits > 36;
+    m.mu32 = m.big ? (uint32_t)((((nt::u128)1) << 64) / q) : 0;
+    (void)log_n;
+    return m;
+}
+
+extern "C" int b200fhe_ctx_create_empty(int log_n, int L, int device, b200fhe_ctx** out) {
+    if (!out) return b200_set_err(B200FHE_EINVAL, "null out");
+    if (log_n < 1 || log_n > 17) return b200_set_err(B200FHE_EUNSUPPORTED, "log_n=%d unsupported (1..17)", log_n);
+    if (L < 1 || L > 4096) return b200_set_err(B200FHE_EINVAL, "L=%d out of range", L);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return b200_set_err(B200FHE_ECUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return b200_set_err(B200FHE_EINVAL, "device %d of %d", device, ndev);
+    CK(cudaSetDevice(device));
+    b200fhe_ctx* c = new b200fhe_ctx();
+    c->log_n = log_n;
+    c->N = (size_t)1 << log_n;
+    c->L = L;
+    c->device = device;
+    c->moduli.assign(L, 0);
+    c->psi.assign(L, 0);
+    c->h_mods.resize(L);
+    memset(c->h_mods.data(), 0, sizeof(B200Mod) * L);
+    c->has_inverse.assign(L, 0);
+    cudaError_t e = cudaMalloc(&c->d_mods, sizeof(B200Mod) * L);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_tw, sizeof(ulonglong2) * c->N * L);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_itw, sizeof(ulonglong2) * c->N * L);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        b200fhe_ctx_destroy(c);
+        return b200_set_err(e == cudaErrorMemoryAllocation ? B200FHE_ENOMEM : B200FHE_ECUDA, "ctx alloc: %s", cudaGetErrorString(e));
+    }
+    *out = c;
+    return 0;
+}
+
+extern "C" int b200fhe_ctx_set_tables(b200fhe_ctx* c, int idx, uint64_t q, const uint64_t* tw, const uint64_t* tws,
+                                      const uint64_t* itw, const uint64_t* itws, uint64_t n_inv, uint64_t n_inv_shoup,
+                                      void* stream) {
+    if (!c || idx < 0 || idx >= c->L || !tw || !tws) return b200_set_err(B200FHE_EINVAL, "set_tables: bad args");
+    if (q < 3 || (q >> 60)) return b200_set_err(B200FHE_EINVAL, "modulus %llu outside (2, 2^60)", (unsigned long long)q);
+    (void)n_inv_shoup;
+    CK(cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t N = c->N;
+    std::vector<ulonglong2> buf(N);
+    for (size_t i = 0; i < N; i++) buf[i] = make_ulonglong2(tw[i], tws[i]);
+    CK(cudaMemcpyAsync(c->d_tw + (size_t)idx * N, buf.data(), sizeof(ulonglong2) * N, cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));
+    uint64_t itw1 = 0;
+    if (itw && itws) {
+        for (size_t i = 0; i < N; i++) buf[i] = make_ulonglong2(itw[i], itws[i]);
+        CK(cudaMemcpyAsync(c->d_itw + (size_t)idx * N, buf.data(), sizeof(ulonglong2) * N, cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));
+        itw1 = N > 1 ? itw[1] : 1;
+        c->has_inverse[idx] = 1;
+        if (!n_inv) n_inv = nt::invmod(N % q, q);
+    } else {
+        c->has_inverse[idx] = 0;
+    }
+    c->moduli[idx] = q;
+    c->h_mods[idx] = make_mod(q, c->log_n, itw1, n_inv);
+    CK(cudaMemcpyAsync(c->d_mods + idx, &c->h_mods[idx], sizeof(B200Mod), cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+extern "C" int b200fhe_ctx_create(int log_n, const uint64_t* moduli, int L, int device, b200fhe_ctx** out) {
+    if (!moduli) return b200_set_err(B200FHE_EINVAL, "null moduli");
+    const uint64_t N = (uint64_t)1 << log_n;
+    for (int i = 0; i < L; i++) {
+        uint64_t q = moduli[i];
+        if (q < 3 || (q >> 60) || (q - 1) % (2 * N) || !nt::is_prime(q))
+            return b200_set_err(B200FHE_EINVAL, "modulus[%d]=%llu must be a prime < 2^60 with q = 1 mod 2N", i, (unsigned long long)q);
+    }
+    int rc = b200fhe_ctx_create_empty(log_n, L, device, out);
+    if (rc) return rc;
+    std::vector<uint64_t> rp(N), rps(N), irp(N), irps(N);
+    for (int i = 0; i < L; i++) {
+        uint64_t q = moduli[i], psi = nt::min_primitive_root(2 * N, q);
+        if (!psi) { b200fhe_ctx_destroy(*out); *out = nullptr; return b200_set_err(B200FHE_EINVAL, "no root for modulus %d", i); }
+        nt::tables(log_n, q, psi, rp.data(), rps.data(), irp.data(), irps.data());
+        uint64_t ni = nt::invmod(N % q, q);
+        rc = b200fhe_ctx_set_tables(*out, i, q, rp.data(), rps.data(), irp.data(), irps.data(), ni, nt::shoup(ni, q), nullptr);
+        if (rc) { b200fhe_ctx_destroy(*out); *out = nullptr; return rc; }
+        (*out)->psi[i] = psi;
+    }
+    return 0;
+}
+
+extern "C" int b200fhe_ctx_destroy(b200fhe_ctx* c) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    if (c->d_mods) cudaFree(c->d_mods);
+    if (c->d_tw) cudaFree(c->d_tw);
+    if (c->d_itw) cudaFree(c->d_itw);
+    if (c->d_stage) cudaFree(c->d_stage);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
+    if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
+    for (auto e : c->ev) cudaEventDestroy(e);
+    delete c;
+    return 0;
+}
+extern "C" int b200fhe_ctx_info(const b200fhe_ctx* c, int* log_n, int* L, int* device) {
+    if (!c) return b200_set_err(B200FHE_EINVAL, "null ctx");
+    if (log_n) *log_n = c->log_n;
+    if (L) *L = c->L;
+    if (device) *device = c->device;
+    return 0;
+}
+extern "C" int b200fhe_ctx_moduli(const b200fhe_ctx* c, uint64_t* out) {
+    if (!c || !out) return b200_set_err(B200FHE_EINVAL, "null arg");
+    memcpy(out, c->moduli.data(), sizeof(uint64_t) * c->L);
+    return 0;
+}
+
+// ---------------------------------------------------------------- transforms
+static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py's gpu_launches)
+extern "C" unsigned long long b200fhe_launch_count(void) { return g_launches; }
+
+// Polynomials per launch pair: the column and row passes of one chunk run
+// back to back so the lazily-reduced intermediate stays in the 126 MB L2
+// instead of making a second HBM round trip.
+static size_t chunk_polys(const b200fhe_ctx* c, size_t L) {
+    const size_t bytes_per_poly = L * c->N * sizeof(uint64_t);
+    const size_t budget = (size_t)40 << 20;
+    size_t n = budget / (bytes_per_poly ? bytes_per_poly : 1);
+    return n ? n : 1;
+}
+
+static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, size_t L, size_t start, int mask,
+                   cudaStream_t s) {
+    if (!c || (!d && n_poly && L)) return b200_set_err(B200FHE_EINVAL, "nwt: null argument");
+    if (L == 0 || n_poly == 0) return 0;
+    if (start + L > (size_t)c->L) return b200_set_err(B200FHE_EINVAL, "nwt: start_mod %zu + L %zu exceeds context (%d)", start, L, c->L);
+    bool big = true;
+    for (size_t i = start; i < start + L; i++) {
+        if (!c->moduli[i]) return b200_set_err(B200FHE_EINVAL, "nwt: modulus %zu not set", i);
+        if (inverse && !c->has_inverse[i]) return b200_set_err(B200FHE_EINVAL, "nwt: no inverse tables for modulus %zu", i);
+        big = big && c->h_mods[i].big;
+    }
+    CK(cudaSetDevice(c->device));
+    PassArgs a;
+    a.mods = c->d_mods;
+    a.tw = inverse ? c->d_itw : c->d_tw;
+    a.N = (u32)c->N;
+    a.L = (u32)L;
+    a.start_mod = (u32)start;
+    const size_t step = (mask == 3) ? chunk_polys(c, L) : n_poly;
+    for (size_t p0 = 0; p0 < n_poly; p0 += step) {
+        const size_t np = n_poly - p0 < step ? n_poly - p0 : step;
+        a.data = (u64*)d + p0 * L * c->N;
+        int rc = launch_ntt(inverse, big, a, c->log_n, (u32)(np * L), mask, s);
+        if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt: log_n=%d unsupported (rc=%d)", c->log_n, rc);
+        g_launches += (c->log_n <= 11) ? 1 : ((mask == 3) ? 2 : 1);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200fhe_nwt_forward(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, void* stream) {
+    return run_ntt(c, false, d, n_poly, L, start, 3, (cudaStream_t)stream);
+}
+extern "C" int b200fhe_nwt_backward(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, void* stream) {
+    return run_ntt(c, true, d, n_poly, L, start, 3, (cudaStream_t)stream);
+}
+// measurement hook: one pass (1 = first kernel, 2 = second kernel) of the transform
+extern "C" int b200fhe_debug_nwt_pass(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, int inverse,
+                                      int pass, void* stream) {
+    if (pass != 1 && pass != 2) return b200_set_err(B200FHE_EINVAL, "pass must be 1 or 2");
+    return run_ntt(c, inverse != 0, d, n_poly, L, start, pass, (cudaStream_t)stream);
+}
+
+int b200_ensure_stage(b200fhe_ctx* c, size_t words, bool need_host) {
+    if (c->stage_words < words) {
+        if (c->d_stage) cudaFree(c->d_stage);
+        c->d_stage = nullptr; c->stage_words = 0;
+        CK(cudaMalloc(&c->d_stage, words * sizeof(uint64_t)));
+        c->stage_words = words;
+    }
+    if (need_host && c->hstage_words < words) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr; c->hstage_words = 0;
+        CK(cudaMallocHost(&c->h_stage, words * sizeof(uint64_t)));
+        c->hstage_words = words;
+    }
+    return 0;
+}
+
+extern "C" int b200fhe_host_alloc(void** p, size_t bytes) {
+    if (!p) return b200_set_err(B200FHE_EINVAL, "null out");
+    CK(cudaMallocHost(p, bytes));
+    return 0;
+}
+extern "C" int b200fhe_host_free(void* p) {
+    if (p) CK(cudaFreeHost(p));
+    return 0;
+}
+
+static bool is_pinned(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+// H2D -> kernels -> D2H as in ntt_test.cu:89-102, but chunked per polynomial
+// group and software-pipelined over three streams so the two PCIe directions
+// and the kernels overlap.  Pinned caller buffers are copied directly; pageable
+// ones go through the context's pinned staging buffer.
+static int run_ntt_host(b200fhe_ctx* c, bool inverse, uint64_t* h, size_t n_poly, size_t L, size_t start) {
+    if (!c || (!h && n_poly && L)) return b200_set_err(B200FHE_EINVAL, "nwt_host: null argument");
+    if (n_poly == 0 || L == 0) return 0;
+    CK(cudaSetDevice(c->device));
+    const size_t poly_words = L * c->N, words = n_poly * poly_words;
+    const bool pinned = is_pinned(h);
+    int rc = b200_ensure_stage(c, words, !pinned);
+    if (rc) return rc;
+    uint64_t* src = h;
+    if (!pinned) { memcpy(c->h_stage, h, words * sizeof(uint64_t)); src = c->h_stage; }
+    if (!c->s_h2d) {
+        CK(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+    }
+    const size_t step = chunk_polys(c, L);
+    const size_t n_chunks = (n_poly + step - 1) / step;
+    if (c->ev.size() < 2 * n_chunks) {
+        size_t old = c->ev.size();
+        c->ev.resize(2 * n_chunks);
+        for (size_t i = old; i < c->ev.size(); i++) CK(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
+    }
+    cudaStream_t sk = c->own_stream;
+    for (size_t k = 0; k < n_chunks; k++) {
+        const size_t p0 = k * step, np = n_poly - p0 < step ? n_poly - p0 : step;
+        const size_t off = p0 * poly_words, cnt = np * poly_words;
+        CK(cudaMemcpyAsync(c->d_stage + off, src + off, cnt * sizeof(uint64_t), cudaMemcpyHostToDevice, c->s_h2d));
+        CK(cudaEventRecord(c->ev[2 * k], c->s_h2d));
+        CK(cudaStreamWaitEvent(sk, c->ev[2 * k], 0));
+        rc = run_ntt(c, inverse, c->d_stage + off, np, L, start, 3, sk);
+        if (rc) return rc;
+        CK(cudaEventRecord(c->ev[2 * k + 1], sk));
+        CK(cudaStreamWaitEvent(c->s_d2h, c->ev[2 * k + 1], 0));
+        CK(cudaMemcpyAsync(src + off, c->d_stage + off, cnt * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->s_d2h));
+    }
+    CK(cudaStreamSynchronize(c->s_d2h));
+    if (!pinned) memcpy(h, c->h_stage, words * sizeof(uint64_t));
+    return 0;
+}
+extern "C" int b200fhe_nwt_forward_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start) {
+    return run_ntt_host(c, false, h, n_poly, L, start);
+}
+extern "C" int b200fhe_nwt_backward_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start) {
+    return run_ntt_host(c, true, h, n_poly, L, start);
+}
+
+// ---------------------------------------------------------------- fault injection
+__global__ void k_flip_bit(u64* data, size_t idx, unsigned bit) { data[idx] ^= (1ull << bit); }
+
+extern "C" int b200fhe_flip_bit(uint64_t* d, size_t idx, unsigned bit, void* stream) {
+    if (!d || bit > 63) return b200_set_err(B200FHE_EINVAL, "flip_bit: bad args");
+    k_flip_bit<<<1, 1, 0, (cudaStream_t)stream>>>((u64*)d, idx, bit);
+    CK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,49 @@
+// Host-side context shared by the CUDA translation units and the C ABI.
+// Mirrors what the reference harness assembles by hand from Phantom types
+// (reliability_test/ntt_test.cu:44-69: CoeffModulus::Create -> DModulus[] ->
+// DNTTTable.init/set per limb): moduli, Barrett/Shoup constants and the
+// bit-reversed twiddle tables, resident on one device.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "modarith.cuh"
+
+namespace b200 {
+
+struct PassArgs {
+    u64* data;                // [n_limbs][N]
+    const B200Mod* mods;      // [ctx.L]
+    const ulonglong2* tw;     // [ctx.L][N] interleaved (w, w_shoup), forward or inverse table
+    u32 N;
+    u32 L;                    // limbs per polynomial in this call
+    u32 start_mod;
+};
+
+// mask: 1 = first pass only, 2 = second pass only, 3 = whole transform
+int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s);
+
+}  // namespace b200
+
+struct b200fhe_ctx {
+    int log_n = 0;
+    size_t N = 0;
+    int L = 0;                       // number of moduli held
+    int device = 0;
+    std::vector<uint64_t> moduli;
+    std::vector<uint64_t> psi;       // minimal primitive 2N-th roots
+    std::vector<B200Mod> h_mods;
+    std::vector<uint8_t> has_inverse;   // per modulus: inverse tables present
+    B200Mod* d_mods = nullptr;       // [L]
+    ulonglong2* d_tw = nullptr;      // [L][N] forward (w, w')
+    ulonglong2* d_itw = nullptr;     // [L][N] inverse
+    // host-buffer entry points: pinned staging + device scratch, grown on demand
+    uint64_t* h_stage = nullptr;
+    uint64_t* d_stage = nullptr;
+    size_t stage_words = 0, hstage_words = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    std::vector<cudaEvent_t> ev;
+};

@@ -1,0 +1,261 @@
+// Batched negacyclic NTT / INTT over RNS limbs, hand-written for sm_100a.
+//
+// Replaces phantom-fhe's nwt_2d_radix8_forward_inplace / backward (call sites
+// reliability_test/ntt_test.cu:95,144; definition absent from the reference
+// tree) with SEAL ntt_negacyclic_harvey semantics: forward natural -> bit-
+// reversed, inverse bit-reversed -> natural scaled by N^-1, canonical outputs.
+//
+// Structure (N = CL x 256, 2^12 <= N <= 2^17): the limb is a CL x 256 matrix.
+//   forward : column pass (first log2 CL stages, twiddles shared by all columns)
+//             then row pass (last 8 stages, per-row twiddles, contiguous rows);
+//   inverse : row pass then column pass (N^-1 folded into the last stage).
+// Each pass keeps 16/32 coefficients per thread in registers for a radix-16/32
+// phase, exchanges once through shared memory, and runs the second phase.
+// Intermediates are stored lazily (< 16q); only final outputs are canonical.
+#include "ntt_phases.cuh"
+#include "ctx.hpp"
+
+namespace b200 {
+
+constexpr int kRowLog = 8;          // row length 256
+constexpr int kRowLen = 1 << kRowLog;
+constexpr int kTile = 16;           // columns per column-pass CTA / rows per row-pass CTA
+
+__device__ __forceinline__ int swz(int c) { return (c & ~15) | ((c ^ (c >> 4)) & 15); }
+
+
+// ---------------------------------------------------------------- forward, columns
+template <int LC, int LA, bool BIG>
+__global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
+k_fwd_col(PassArgs p) {
+    constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
+    extern __shared__ u64 sm[];
+    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    const B200Mod m = p.mods[mi];
+    const ulonglong2* tw = p.tw + (size_t)mi * p.N;
+    u64* base = p.data + (size_t)limb * p.N + blockIdx.x * kTile;
+    const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
+    if (g < RB) {
+        u64 v[RA];
+#pragma unroll
+        for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
+        ct_phase<LA, BIG>(v, tw, 1u, m);
+        if (LB > 0) {
+#pragma unroll
+            for (int e = 0; e < RA; e++) sm[(e * RB + g) * kTile + c] = v[e];
+        } else {
+#pragma unroll
+            for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
+        }
+    }
+    if constexpr (LB > 0) {
+        __syncthreads();
+        if (g < RA) {
+            u64 w[RB];
+#pragma unroll
+            for (int e = 0; e < RB; e++) w[e] = sm[(g * RB + e) * kTile + c];
+            ct_phase<LB, BIG>(w, tw, (1u << LA) + g, m);
+#pragma unroll
+            for (int e = 0; e < RB; e++) base[(size_t)(g * RB + e) * kRowLen + c] = w[e];
+        }
+    }
+}
+
+// ---------------------------------------------------------------- forward, rows
+template <bool BIG>
+__global__ void __launch_bounds__(256) k_fwd_row(PassArgs p) {
+    __shared__ u64 sm[kTile * kRowLen];
+    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    const B200Mod m = p.mods[mi];
+    const ulonglong2* tw = p.tw + (size_t)mi * p.N;
+    const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
+    const u32 row = blockIdx.x * kTile + rl;
+    const u32 P = (p.N >> kRowLog) + row;
+    u64* rowp = p.data + (size_t)limb * p.N + (size_t)row * kRowLen;
+    u64 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = rowp[e * 16 + cl];
+    ct_phase<4, BIG>(v, tw, P, m);
+#pragma unroll
+    for (int e = 0; e < 16; e++) sm[rl * kRowLen + swz(e * 16 + cl)] = v[e];
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = sm[rl * kRowLen + swz(cl * 16 + e)];
+    ct_phase<4, BIG>(v, tw, (P << 4) + cl, m);
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = canon3(reduce_lazy<BIG>(v[e], m), m.q);
+    ulonglong2* out = reinterpret_cast<ulonglong2*>(rowp + cl * 16);
+#pragma unroll
+    for (int e = 0; e < 8; e++) out[e] = make_ulonglong2(v[2 * e], v[2 * e + 1]);
+}
+
+// ---------------------------------------------------------------- inverse, rows
+template <bool BIG>
+__global__ void __launch_bounds__(256) k_inv_row(PassArgs p) {
+    __shared__ u64 sm[kTile * kRowLen];
+    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    const B200Mod m = p.mods[mi];
+    const ulonglong2* itw = p.tw + (size_t)mi * p.N;
+    const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
+    const u32 row = blockIdx.x * kTile + rl;
+    const u32 P = (p.N >> kRowLog) + row;
+    u64* rowp = p.data + (size_t)limb * p.N + (size_t)row * kRowLen;
+    u64 v[16];
+    const ulonglong2* in = reinterpret_cast<const ulonglong2*>(rowp + cl * 16);
+#pragma unroll
+    for (int e = 0; e < 8; e++) { ulonglong2 x = in[e]; v[2 * e] = x.x; v[2 * e + 1] = x.y; }
+    gs_phase<4, BIG, false>(v, itw, (P << 4) + cl, m);
+#pragma unroll
+    for (int e = 0; e < 16; e++) sm[rl * kRowLen + swz(cl * 16 + e)] = v[e];
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = sm[rl * kRowLen + swz(e * 16 + cl)];
+    gs_phase<4, BIG, false>(v, itw, P, m);
+#pragma unroll
+    for (int e = 0; e < 16; e++) rowp[e * 16 + cl] = v[e];
+}
+
+// ---------------------------------------------------------------- inverse, columns
+template <int LC, int LA, bool BIG>
+__global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
+k_inv_col(PassArgs p) {
+    constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
+    extern __shared__ u64 sm[];
+    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    const B200Mod m = p.mods[mi];
+    const ulonglong2* itw = p.tw + (size_t)mi * p.N;
+    u64* base = p.data + (size_t)limb * p.N + blockIdx.x * kTile;
+    const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
+    if constexpr (LB > 0) {
+        if (g < RA) {
+            u64 w[RB];
+#pragma unroll
+            for (int e = 0; e < RB; e++) w[e] = base[(size_t)(g * RB + e) * kRowLen + c];
+            gs_phase<LB, BIG, false>(w, itw, (1u << LA) + g, m);
+#pragma unroll
+            for (int e = 0; e < RB; e++) sm[(g * RB + e) * kTile + c] = w[e];
+        }
+        __syncthreads();
+    }
+    if (g < RB) {
+        u64 v[RA];
+        if (LB > 0) {
+#pragma unroll
+            for (int e = 0; e < RA; e++) v[e] = sm[(e * RB + g) * kTile + c];
+        } else {
+#pragma unroll
+            for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
+        }
+        gs_phase<LA, BIG, true>(v, itw, 1u, m);
+#pragma unroll
+        for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
+    }
+}
+
+// ---------------------------------------------------------------- small N (2 <= N <= 2^11)
+// One CTA per limb, whole limb in shared memory, radix-2 stages, fully reduced.
+// Serves the prototype-sized cases (N = 16 .. 2048) of the Python bindings.
+template <bool INVERSE>
+__global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
+    extern __shared__ u64 a[];
+    const u32 limb = blockIdx.x, mi = p.start_mod + limb % p.L;
+    const B200Mod m = p.mods[mi];
+    const ulonglong2* tw = p.tw + (size_t)mi * p.N;
+    u64* base = p.data + (size_t)limb * p.N;
+    const u32 N = p.N, q_unused = 0; (void)q_unused;
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon3(reduce_lazy<false>(base[i], m), m.q);
+    __syncthreads();
+    if (!INVERSE) {
+        for (int s = 0; s < logn; s++) {
+            const u32 t = N >> (s + 1), mm = 1u << s;
+            for (u32 b = threadIdx.x; b < N / 2; b += blockDim.x) {
+                const u32 i = b / t, j = b % t, x = 2 * i * t + j;
+                const ulonglong2 W = tw[mm + i];
+                const u64 X = a[x], T = canon2(shoup_mul(a[x + t], W.x, W.y, m.q), m.q);
+                a[x] = canon2(X + T, m.q);
+                a[x + t] = canon2(X + m.q - T, m.q);
+            }
+            __syncthreads();
+        }
+    } else {
+        for (int s = logn - 1; s >= 0; s--) {
+            const u32 t = N >> (s + 1), mm = 1u << s;
+            for (u32 b = threadIdx.x; b < N / 2; b += blockDim.x) {
+                const u32 i = b / t, j = b % t, x = 2 * i * t + j;
+                const ulonglong2 W = tw[mm + i];
+                const u64 U = a[x], V = a[x + t];
+                a[x] = canon2(U + V, m.q);
+                a[x + t] = canon2(shoup_mul(U + m.q - V, W.x, W.y, m.q), m.q);
+            }
+            __syncthreads();
+        }
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon2(shoup_mul(a[i], m.ninv, m.ninv_s, m.q), m.q);
+        __syncthreads();
+    }
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) base[i] = a[i];
+}
+
+// ---------------------------------------------------------------- dispatch
+template <int LC, int LA, bool BIG>
+static void launch_fwd2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
+    constexpr int LB = LC - LA;
+    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kTile, n_limbs);
+    constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (mask & 1) k_fwd_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
+    if (mask & 2) k_fwd_row<BIG><<<gr, 256, 0, s>>>(a);
+}
+template <int LC, int LA, bool BIG>
+static void launch_inv2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
+    constexpr int LB = LC - LA;
+    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kTile, n_limbs);
+    if (mask & 1) k_inv_row<BIG><<<gr, 256, 0, s>>>(a);
+    constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_inv_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (mask & 2) k_inv_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
+}
+
+template <bool BIG>
+static int launch_ntt_t(bool inverse, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
+#define B200_CASE(LOGN, LC, LA)                                              \
+    case LOGN:                                                               \
+        if (inverse) launch_inv2<LC, LA, BIG>(a, n_limbs, mask, s);                \
+        else launch_fwd2<LC, LA, BIG>(a, n_limbs, mask, s);                        \
+        return 0;
+    switch (logn) {
+        B200_CASE(12, 4, 4)
+        B200_CASE(13, 5, 3)
+        B200_CASE(14, 6, 3)
+        B200_CASE(15, 7, 4)
+        B200_CASE(16, 8, 4)
+        B200_CASE(17, 9, 5)
+    }
+#undef B200_CASE
+    return -1;
+}
+
+// Launch the transform on n_limbs limbs ([n_poly][L][N], limb l of each poly
+// uses modulus start_mod + l).  Returns 0, or <0 if logn is unsupported.
+int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
+    if (n_limbs == 0) return 0;
+    if (logn >= 1 && logn <= 11) {
+        size_t smem = sizeof(u64) << logn;
+        if (inverse) k_small<true><<<n_limbs, 256, smem, s>>>(a, logn);
+        else k_small<false><<<n_limbs, 256, smem, s>>>(a, logn);
+        return 0;
+    }
+    // grid.y limit is 65535 limbs per launch: split long batches
+    const u32 kMaxY = 32768;
+    for (u32 off = 0; off < n_limbs; off += kMaxY) {
+        PassArgs b = a;
+        b.data = a.data + (size_t)off * a.N;
+        // keep limb->modulus mapping: off must be a multiple of L
+        u32 cnt = n_limbs - off < kMaxY ? n_limbs - off : kMaxY;
+        if (off % a.L) return -2;
+        int rc = big ? launch_ntt_t<true>(inverse, b, logn, cnt, mask, s) : launch_ntt_t<false>(inverse, b, logn, cnt, mask, s);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+}  // namespace b200

@@ -1,0 +1,122 @@
+/*
+ * b200fhe.h -- C ABI of the B200-native FHE reliability hot path.
+ *
+ * Drop-in boundary for the arithmetic that Stardust-lf/fhe-reliability-gpu
+ * obtains from libPhantom.so (C++ ABI, missing from the reference tree).  Every
+ * entry point names the reference interface it replaces (paths relative to the
+ * reference root).  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Conventions: all functions return 0 on success or a negative B200FHE_E* code;
+ * b200fhe_last_error() returns a thread-local message for the last failure.
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream).  Device
+ * pointers are marked d_, host pointers h_.  Polynomials are row-major
+ * [n_poly][L][N] uint64 words; limb l of every polynomial uses modulus
+ * start_mod + l of the context (Phantom's `start_modulus_idx`).
+ * There is no CPU fallback: a call without a usable CUDA device fails with
+ * B200FHE_ECUDA.
+ */
+#ifndef B200FHE_H
+#define B200FHE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200FHE_OK 0
+#define B200FHE_EINVAL (-1)   /* bad argument (mirrors ntt_test.cu:29-38 argv checks -> exit(1)) */
+#define B200FHE_ECUDA (-2)    /* CUDA runtime error / no device */
+#define B200FHE_ENOMEM (-3)
+#define B200FHE_EUNSUPPORTED (-4)
+
+typedef struct b200fhe_ctx b200fhe_ctx;
+
+int b200fhe_version(void);
+const char* b200fhe_last_error(void);
+
+/* ---- host-side number theory (no GPU needed) --------------------------- */
+
+/* phantom::arith::CoeffModulus::Create(N, bit_sizes) (ntt_test.cu:44,
+ * dotprod_test.cu:200): for each bit size the largest primes < 2^bits with
+ * p = 1 mod 2N, handed out smallest-first.  out[n]. */
+int b200fhe_primes_create(uint64_t N, const int* bits, int n, uint64_t* out);
+
+/* SEAL try_minimal_primitive_root(2N, q): the smallest primitive 2N-th root. */
+int b200fhe_min_primitive_root(uint64_t N, uint64_t q, uint64_t* psi);
+
+/* phantom::arith::NTT(log_n, modulus) + get_from_root_powers() /
+ * get_from_root_powers_shoup() (ntt_test.cu:60-64): rp[bitrev(i)] = psi^i and
+ * its Shoup quotients floor(w 2^64/q); irp[bitrev(i)] = psi^-i; n_inv = N^-1.
+ * Any output pointer may be NULL.  Arrays have N = 2^log_n words. */
+int b200fhe_host_tables(int log_n, uint64_t q, uint64_t* rp, uint64_t* rp_shoup, uint64_t* irp,
+                        uint64_t* irp_shoup, uint64_t* n_inv, uint64_t* n_inv_shoup);
+
+/* Modulus::const_ratio() (ntt_test.cu:51-52): floor(2^128/q) as two words. */
+int b200fhe_const_ratio(uint64_t q, uint64_t ratio[2]);
+
+/* ---- context ------------------------------------------------------------ */
+
+/* Builds, for L moduli, everything ntt_test.cu:44-69 builds by hand (DModulus
+ * array, DNTTTable.init + per-limb set with forward AND inverse tables) on
+ * `device`.  Requires 1 <= log_n <= 17, 2 < q < 2^60, q = 1 mod 2N, q prime. */
+int b200fhe_ctx_create(int log_n, const uint64_t* moduli, int L, int device, b200fhe_ctx** out);
+
+/* DNTTTable::init(N, L, stream) (ntt_test.cu:57-58): empty context whose limbs
+ * are filled by b200fhe_ctx_set_tables. */
+int b200fhe_ctx_create_empty(int log_n, int L, int device, b200fhe_ctx** out);
+
+/* DNTTTable::set(&modulus[i], tw, tw_shoup, itw, itw_shoup, n_inv, n_inv_shoup,
+ * idx, stream) (ntt_test.cu:61-68).  Host tables are copied.  itw/itw_shoup may
+ * be NULL (the harness passes nullptr): the backward transform on that limb
+ * then fails with B200FHE_EINVAL.  itw uses this library's layout
+ * itw[bitrev(i)] = psi^-i (b200fhe_host_tables produces it). */
+int b200fhe_ctx_set_tables(b200fhe_ctx* ctx, int idx, uint64_t q, const uint64_t* tw, const uint64_t* tw_shoup,
+                           const uint64_t* itw, const uint64_t* itw_shoup, uint64_t n_inv, uint64_t n_inv_shoup,
+                           void* stream);
+
+int b200fhe_ctx_destroy(b200fhe_ctx* ctx);
+int b200fhe_ctx_info(const b200fhe_ctx* ctx, int* log_n, int* L, int* device);
+int b200fhe_ctx_moduli(const b200fhe_ctx* ctx, uint64_t* out /*[L]*/);
+
+/* ---- the hot path --------------------------------------------------------- */
+
+/* nwt_2d_radix8_forward_inplace(inout, tables, coeff_modulus_size, start_modulus_idx,
+ * stream) (ntt_test.cu:95,144; ntt_real_test.cu:89,126).  In-place forward
+ * negacyclic NTT, natural order in -> bit-reversed out, outputs in [0,q).
+ * Input words are taken mod q (documented deviation for bit-flipped words). */
+int b200fhe_nwt_forward(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_poly, size_t L, size_t start_mod, void* stream);
+
+/* nwt_2d_radix8_backward_inplace / SEAL inverse_ntt_negacyclic_harvey (reached
+ * inside multiply/relinearize/decrypt, dotprod_test.cu:113-119): bit-reversed
+ * in -> natural out, scaled by N^-1, outputs in [0,q). */
+int b200fhe_nwt_backward(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_poly, size_t L, size_t start_mod, void* stream);
+
+/* Same transforms on HOST buffers: the H2D copy, the kernels and the D2H copy
+ * of ntt_test.cu:89-102 in one call (pinned staging inside the context),
+ * synchronous on return. */
+int b200fhe_nwt_forward_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly, size_t L, size_t start_mod);
+int b200fhe_nwt_backward_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly, size_t L, size_t start_mod);
+
+/* Pinned host memory for the *_host entry points (what Phantom's
+ * make_cuda_auto_ptr / cudaMallocHost staging gives the harness).  Buffers from
+ * here (or any cudaHostRegister'ed memory) are DMA'd directly; pageable buffers
+ * are staged through a pinned buffer inside the context. */
+int b200fhe_host_alloc(void** p, size_t bytes);
+int b200fhe_host_free(void* p);
+
+/* Measurement hooks (bench.py): one pass of the two-kernel transform
+ * (pass 1 = first kernel, 2 = second), and the number of kernels this library
+ * has launched in this process. */
+int b200fhe_debug_nwt_pass(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_poly, size_t L, size_t start_mod, int inverse,
+                           int pass, void* stream);
+unsigned long long b200fhe_launch_count(void);
+
+/* _flip_bit_kernel<<<1,1>>>(data, idx, bit) (dotprod_test.cu:31-33,55):
+ * d_data[idx] ^= 1 << bit. */
+int b200fhe_flip_bit(uint64_t* d_data, size_t idx, unsigned bit, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200FHE_H */
