@@ -56,6 +56,7 @@ def lib():
             ("orc_bconv_proto", None, [U64P, U64P, i32, i32, u64, U64P, U64P]),
             ("orc_root_of_unity", u64, [u64, u64, u64]),
             ("orc_cyclic_ntt_direct", None, [U64P, U64P, u64, u64, u64]),
+            ("orc_cyclic_ntt_radix2", None, [U64P, u64, u64, u64]),
             ("orc_four_step_cyclic", i32, [U64P, U64P, u64, u64, u64, U64P, U64P]),
             ("orc_protection_check_blockdiag", i32, [U64P, U64P, u64, u64, u64, u64, U64P, U64P]),
         ]:
@@ -177,6 +178,13 @@ def cyclic_ntt_direct(a, N, mod, g):
     a = np.ascontiguousarray(a, dtype=np.uint64); y = np.zeros(N, dtype=np.uint64)
     lib().orc_cyclic_ntt_direct(_p(a), _p(y), N, mod, g)
     return y
+
+
+def cyclic_ntt_radix2(a, mod, root):
+    """motivation/ntt.py:8-32 ntt(a, mod, root)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64).copy()
+    lib().orc_cyclic_ntt_radix2(_p(a), len(a), mod, root)
+    return a
 
 
 def four_step_cyclic(a, N, mod, g):

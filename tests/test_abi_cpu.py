@@ -1,0 +1,79 @@
+"""CPU tier: the C-ABI library loads, exports every symbol include/b200fhe.h declares,
+its host-side number theory agrees with the oracle, and compute entry points fail
+loudly (no CPU fallback) when no CUDA device is present."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    out = set()
+    inc = os.path.join(ROOT, "include")
+    for f in os.listdir(inc):
+        if f.endswith(".h"):
+            txt = re.sub(r"/\*.*?\*/", "", open(os.path.join(inc, f)).read(), flags=re.S)
+            out |= set(re.findall(r"\b(b200fhe_[a-z0-9_]+)\s*\(", txt))
+    return out
+
+
+def test_every_declared_symbol_is_exported_and_bound(pkg):
+    syms = declared_symbols()
+    assert len(syms) >= 20
+    raw = C.CDLL(pkg.LIB_PATH)
+    for s in sorted(syms):
+        assert hasattr(raw, s), "libb200fhe.so does not export %s" % s
+    from fhe_reliability_gpu_b200 import binding
+    assert syms == set(binding.SIGNATURES), sorted(syms ^ set(binding.SIGNATURES))
+
+
+def test_product_never_imports_the_oracle():
+    pk = os.path.join(ROOT, "fhe_reliability_gpu_b200")
+    for dp, _, fs in os.walk(pk):
+        if "/build" in dp or "/lib" in dp:
+            continue
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")) or f == "Makefile":
+                txt = open(os.path.join(dp, f), errors="ignore").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle|liboracle|#include\s+\"[^\"]*oracle", txt, re.M), \
+                    os.path.join(dp, f)
+
+
+def test_host_number_theory_matches_oracle(pkg, O):
+    assert pkg.primes_create(16384, [50] * 6) == O.primes_create(16384, [50] * 6)
+    for logn, bits in [(4, 30), (10, 50), (12, 60), (16, 60)]:
+        N = 1 << logn
+        q = pkg.primes_create(N, [bits])[0]
+        assert q == O.primes_create(N, [bits])[0]
+        assert pkg.min_primitive_root(N, q) == O.min_root(N, q)
+        rp, rps, irp, irps, ni, nis = pkg.host_tables(logn, q)
+        t = O.Tables(logn, q)
+        assert np.array_equal(rp, t.rp) and np.array_equal(rps, t.rps)
+        assert np.array_equal(irp, t.irp) and np.array_equal(irps, t.irps)
+        assert ni == pow(N, -1, q) and nis == (ni << 64) // q
+        r = (C.c_uint64 * 2)()
+        assert pkg.lib().b200fhe_const_ratio(q, r) == 0
+        assert (r[1] << 64) | r[0] == (1 << 128) // q
+
+
+def test_bad_arguments_are_rejected(pkg):
+    L = pkg.lib()
+    out = (C.c_uint64 * 4)()
+    assert L.b200fhe_primes_create(1000, (C.c_int * 1)(50), 1, out) < 0       # N not a power of two
+    assert L.b200fhe_primes_create(1 << 12, (C.c_int * 1)(14), 1, out) < 0    # no 14-bit prime = 1 mod 8192
+    assert b"prime" in L.b200fhe_last_error() or L.b200fhe_last_error()
+    psi = C.c_uint64()
+    assert L.b200fhe_min_primitive_root(1 << 12, 97, C.byref(psi)) < 0
+
+
+def test_no_cpu_fallback_without_a_device(pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(pkg.B200FHEError) as e:
+        pkg.Context(12, pkg.primes_create(4096, [60]))
+    assert "no CUDA device" in str(e.value) or "CUDA" in str(e.value)
