@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200fhe.so")
+LIB_PATH = os.environ.get("B200FHE_LIB") or os.path.join(_HERE, "lib", "libb200fhe.so")   # env override: A/B builds
 _lib = None
 
 u64, i32, sz, vp = C.c_uint64, C.c_int, C.c_size_t, C.c_void_p

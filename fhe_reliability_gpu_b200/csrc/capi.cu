@@ -73,7 +73,8 @@ static B200Mod make_mod(uint64_t q, int log_n, uint64_t itw1, uint64_t n_inv) {
     m.ratio1 = r[1];
     m.bits = nt::bitlen(q);
     m.big = m.bits > 36;
-    m.mu32 = m.big ? (uint32_t)((((nt::u128)1) << 64) / q) : 0;
+    m.mprec = m.big ? (uint32_t)((((nt::u128)1) << (m.bits + 31)) / q) : 0;
+    m.pshift = m.big ? m.bits - 33 : 0;
     (void)log_n;
     return m;
 }
@@ -100,6 +101,8 @@ extern "C" int b200fhe_ctx_create_empty(int log_n, int L, int device, b200fhe_ct
     cudaError_t e = cudaMalloc(&c->d_mods, sizeof(B200Mod) * L);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_tw, sizeof(ulonglong2) * c->N * L);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_itw, sizeof(ulonglong2) * c->N * L);
+    if (e == cudaSuccess && log_n >= 12) e = cudaMalloc(&c->d_rtw, sizeof(ulonglong2) * c->N * L);
+    if (e == cudaSuccess && log_n >= 12) e = cudaMalloc(&c->d_irtw, sizeof(ulonglong2) * c->N * L);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         b200fhe_ctx_destroy(c);
@@ -107,6 +110,27 @@ extern "C" int b200fhe_ctx_create_empty(int log_n, int L, int device, b200fhe_ct
     }
     *out = c;
     return 0;
+}
+
+// Row-pass tiles (ntt_kernels.cu RowSmem): entries [N/256, N) of a SEAL-layout
+// table regrouped per tile of R = kRowsPerCta rows as A[row][15+pad] (stages
+// 0..3 of the row) followed by B[j][thread] (stages 4..7): 256 R entries per tile.
+static void build_row_tiles(const std::vector<ulonglong2>& tw, size_t N, std::vector<ulonglong2>& out) {
+    const size_t CL = N >> 8, R = b200::kRowsPerCta, TH = R * 16;
+    out.assign(N, make_ulonglong2(0, 0));
+    for (size_t T = 0; T < CL / R; T++) {
+        ulonglong2* tile = out.data() + T * b200::kRowTileEntries;
+        for (size_t rl = 0; rl < R; rl++) {
+            const size_t P = CL + R * T + rl;
+            for (int t = 0; t < 4; t++)
+                for (size_t g = 0; g < ((size_t)1 << t); g++) {
+                    const size_t j = ((size_t)1 << t) - 1 + g;
+                    tile[rl * 16 + j] = tw[(P << t) + g];
+                    for (size_t cl = 0; cl < 16; cl++)
+                        tile[R * 16 + j * TH + rl * 16 + cl] = tw[((((P << 4) + cl)) << t) + g];
+                }
+        }
+    }
 }
 
 extern "C" int b200fhe_ctx_set_tables(b200fhe_ctx* c, int idx, uint64_t q, const uint64_t* tw, const uint64_t* tws,
@@ -122,11 +146,22 @@ extern "C" int b200fhe_ctx_set_tables(b200fhe_ctx* c, int idx, uint64_t q, const
     for (size_t i = 0; i < N; i++) buf[i] = make_ulonglong2(tw[i], tws[i]);
     CK(cudaMemcpyAsync(c->d_tw + (size_t)idx * N, buf.data(), sizeof(ulonglong2) * N, cudaMemcpyHostToDevice, s));
     CK(cudaStreamSynchronize(s));
+    std::vector<ulonglong2> tiles;
+    if (c->d_rtw) {
+        build_row_tiles(buf, N, tiles);
+        CK(cudaMemcpyAsync(c->d_rtw + (size_t)idx * N, tiles.data(), sizeof(ulonglong2) * N, cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));
+    }
     uint64_t itw1 = 0;
     if (itw && itws) {
         for (size_t i = 0; i < N; i++) buf[i] = make_ulonglong2(itw[i], itws[i]);
         CK(cudaMemcpyAsync(c->d_itw + (size_t)idx * N, buf.data(), sizeof(ulonglong2) * N, cudaMemcpyHostToDevice, s));
         CK(cudaStreamSynchronize(s));
+        if (c->d_irtw) {
+            build_row_tiles(buf, N, tiles);
+            CK(cudaMemcpyAsync(c->d_irtw + (size_t)idx * N, tiles.data(), sizeof(ulonglong2) * N, cudaMemcpyHostToDevice, s));
+            CK(cudaStreamSynchronize(s));
+        }
         itw1 = N > 1 ? itw[1] : 1;
         c->has_inverse[idx] = 1;
         if (!n_inv) n_inv = nt::invmod(N % q, q);
@@ -169,6 +204,8 @@ extern "C" int b200fhe_ctx_destroy(b200fhe_ctx* c) {
     if (c->d_mods) cudaFree(c->d_mods);
     if (c->d_tw) cudaFree(c->d_tw);
     if (c->d_itw) cudaFree(c->d_itw);
+    if (c->d_rtw) cudaFree(c->d_rtw);
+    if (c->d_irtw) cudaFree(c->d_irtw);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -220,6 +257,7 @@ static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, siz
     PassArgs a;
     a.mods = c->d_mods;
     a.tw = inverse ? c->d_itw : c->d_tw;
+    a.rtw = inverse ? c->d_irtw : c->d_rtw;
     a.N = (u32)c->N;
     a.L = (u32)L;
     a.start_mod = (u32)start;

@@ -13,10 +13,18 @@
 
 namespace b200 {
 
+// rows of 256 coefficients per row-pass CTA (one row per half-warp); also the tile size of the row table
+#ifndef B200_ROWS_PER_CTA
+#define B200_ROWS_PER_CTA 8
+#endif
+constexpr int kRowsPerCta = B200_ROWS_PER_CTA;
+constexpr int kRowTileEntries = kRowsPerCta * 256;   // ulonglong2 entries per tile: A[rows][16] + B[15][rows*16]
+
 struct PassArgs {
     u64* data;                // [n_limbs][N]
     const B200Mod* mods;      // [ctx.L]
-    const ulonglong2* tw;     // [ctx.L][N] interleaved (w, w_shoup), forward or inverse table
+    const ulonglong2* tw;     // [ctx.L][N] interleaved (w, w_shoup), forward or inverse table (SEAL layout)
+    const ulonglong2* rtw;    // [ctx.L][N] the same table's entries [N/256, N) re-tiled for the row pass
     u32 N;
     u32 L;                    // limbs per polynomial in this call
     u32 start_mod;
@@ -39,6 +47,8 @@ struct b200fhe_ctx {
     B200Mod* d_mods = nullptr;       // [L]
     ulonglong2* d_tw = nullptr;      // [L][N] forward (w, w')
     ulonglong2* d_itw = nullptr;     // [L][N] inverse
+    ulonglong2* d_rtw = nullptr;     // [L][N] forward, row-pass tiles (N >= 2^12)
+    ulonglong2* d_irtw = nullptr;    // [L][N] inverse, row-pass tiles
     // host-buffer entry points: pinned staging + device scratch, grown on demand
     uint64_t* h_stage = nullptr;
     uint64_t* d_stage = nullptr;

@@ -27,29 +27,67 @@ struct __align__(16) B200Mod {
     u64 iw1n_s;   // Shoup quotient of iw1n
     u64 ratio0;   // floor(2^128/q) low word  (DModulus::set arg 2, ntt_test.cu:49-53)
     u64 ratio1;   // floor(2^128/q) high word (DModulus::set arg 3)
-    u32 mu32;     // floor(2^64/q) (fits 32 bits when q >= 2^36): quotient estimate
-    u32 big;      // 1 if q >= 2^36 (fast quotient estimate valid for all 64-bit v)
+    u32 mprec;    // floor(2^(bits+31)/q): normalised 32-bit reciprocal (big moduli)
+    u32 big;      // 1 if q >= 2^36 (32-bit quotient estimate valid for all 64-bit v)
     u32 bits;     // bit length of q
-    u32 pad;
+    u32 pshift;   // bits - 33: floor(v/q) ~ umulhi(v >> 32, mprec) >> pshift
 };
 
-__device__ __forceinline__ u64 shoup_mul(u64 y, u64 w, u64 ws, u64 q) {
-    // y arbitrary 64-bit, w < q, ws = floor(w 2^64 / q)  ->  y*w mod q + {0,q}
-    u64 hi = __umul64hi(y, ws);
-    return y * w - hi * q;
+__device__ __forceinline__ u64 pack64(u32 lo, u32 hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "r"(lo), "r"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack64(u64 v, u32& lo, u32& hi) {
+    asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
 }
 
-// v (any 64-bit when BIG, else any 64-bit too but slower) -> congruent value < 3q
+// y arbitrary 64-bit, w < q, ws = floor(w 2^64 / q), nq = 2^64 - q  ->  y*w mod q + {0,q}.
+// The integer multiplier is the binding pipe of the NTT (profiles/microbench/):
+// the quotient is the exact high word (4 IMAD.WIDE), and the remainder
+// lo64(y*w) + lo64(k*nq) is ONE multiply-add chain (2 IMAD.WIDE + 4 IMAD) with
+// no separate subtraction -- 10 multiplier-pipe instructions, the minimum for an
+// exact 64-bit Shoup product on 32-bit multipliers.
+__device__ __forceinline__ u64 shoup_mul(u64 y, u64 w, u64 ws, u64 nq) {
+    const u64 k = __umul64hi(y, ws);
+    u32 yl, yh, wl, wh, kl, kh, nl, nh, rl, rh;
+    unpack64(y, yl, yh);
+    unpack64(w, wl, wh);
+    unpack64(k, kl, kh);
+    unpack64(nq, nl, nh);
+    u64 r;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(r) : "r"(yl), "r"(wl));
+    asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(r) : "r"(kl), "r"(nl));
+    unpack64(r, rl, rh);
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(yl), "r"(wh));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(yh), "r"(wl));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kl), "r"(nh));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kh), "r"(nl));
+    return pack64(rl, rh);
+}
+
+// v (any 64-bit) -> congruent value < 2q when BIG (q >= 2^36: 32-bit normalised
+// reciprocal, quotient estimate off by at most one), < 3q otherwise.
 template <bool BIG>
 __device__ __forceinline__ u64 reduce_lazy(u64 v, const B200Mod& m) {
     if (BIG) {
-        u32 k = __umulhi((u32)(v >> 32), m.mu32);   // floor(v/q) - {0,1,2}
-        return v - (u64)k * m.q;
+        u32 vl, vh, nl, nh, rl, rh;
+        unpack64(v, vl, vh);
+        unpack64(0 - m.q, nl, nh);
+        const u32 k = __umulhi(vh, m.mprec) >> m.pshift;   // floor(v/q) - {0,1}
+        u64 r;
+        asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(k), "r"(nl), "l"(v));
+        unpack64(r, rl, rh);
+        asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(k), "r"(nh));
+        (void)vl;
+        return pack64(rl, rh);
     } else {
         u64 k = __umul64hi(v, m.bmu);
         return v - k * m.q;
     }
 }
+// bound (in units of q) of reduce_lazy's result
+template <bool BIG> struct LazyBound { static constexpr int value = BIG ? 2 : 3; };
 
 // v < 3q -> [0,q)
 __device__ __forceinline__ u64 canon3(u64 v, u64 q) {

@@ -21,8 +21,34 @@ constexpr int kRowLog = 8;          // row length 256
 constexpr int kRowLen = 1 << kRowLog;
 constexpr int kTile = 16;           // columns per column-pass CTA / rows per row-pass CTA
 
-__device__ __forceinline__ int swz(int c) { return (c & ~15) | ((c ^ (c >> 4)) & 15); }
 
+
+// ---------------------------------------------------------------- TMA helpers
+// 1-D bulk async copy global -> shared, completion counted on an mbarrier.
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, u32 bytes, u64* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
 
 // ---------------------------------------------------------------- forward, columns
 template <int LC, int LA, bool BIG>
@@ -39,7 +65,7 @@ k_fwd_col(PassArgs p) {
         u64 v[RA];
 #pragma unroll
         for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
-        ct_phase<LA, BIG>(v, tw, 1u, m);
+        ct_phase<LA, BIG>(v, TwGlobal{tw, 1u}, m);
         if (LB > 0) {
 #pragma unroll
             for (int e = 0; e < RA; e++) sm[(e * RB + g) * kTile + c] = v[e];
@@ -54,63 +80,108 @@ k_fwd_col(PassArgs p) {
             u64 w[RB];
 #pragma unroll
             for (int e = 0; e < RB; e++) w[e] = sm[(g * RB + e) * kTile + c];
-            ct_phase<LB, BIG>(w, tw, (1u << LA) + g, m);
+            ct_phase<LB, BIG>(w, TwGlobal{tw, (1u << LA) + g}, m);
 #pragma unroll
             for (int e = 0; e < RB; e++) base[(size_t)(g * RB + e) * kRowLen + c] = w[e];
         }
     }
 }
 
-// ---------------------------------------------------------------- forward, rows
+// ---------------------------------------------------------------- row passes
+// One CTA = 16 rows of 256 coefficients of one limb, one row per half-warp, 16
+// coefficients per thread.  The 255 twiddles each row needs (x 16 rows = one
+// 64 KiB tile of the row table, laid out so that every shared-memory read is a
+// conflict-free 128-bit access) arrive by ONE TMA bulk copy that overlaps the
+// coefficient loads; the two radix-16 register phases exchange through a
+// 16-byte-chunk XOR-swizzled shared tile.
+constexpr int kRowThreads = kRowsPerCta * 16;
+struct RowSmem {
+    ulonglong2 twA[kRowsPerCta * 16];    // [row][15 + pad]: stages 0..3 of the row (broadcast reads)
+    ulonglong2 twB[15 * kRowThreads];    // [j][thread]:     stages 4..7, one list per thread
+    u64 x[kRowsPerCta * kRowLen];        // exchange tile
+    u64 bar;
+};
+constexpr u32 kRowTileBytes = sizeof(ulonglong2) * kRowTileEntries;
+constexpr int kRowCtasPerSm = (220 * 1024) / (int)sizeof(RowSmem) > 16 ? 16 : (220 * 1024) / (int)sizeof(RowSmem);
+
 template <bool BIG>
-__global__ void __launch_bounds__(256) k_fwd_row(PassArgs p) {
-    __shared__ u64 sm[kTile * kRowLen];
+__global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs p) {
+    extern __shared__ __align__(128) unsigned char smraw[];
+    RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
     const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
-    const B200Mod m = p.mods[mi];
-    const ulonglong2* tw = p.tw + (size_t)mi * p.N;
     const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
-    const u32 row = blockIdx.x * kTile + rl;
-    const u32 P = (p.N >> kRowLog) + row;
-    u64* rowp = p.data + (size_t)limb * p.N + (size_t)row * kRowLen;
+    if (threadIdx.x == 0) {
+        mbar_init(&s.bar, 1);
+        mbar_expect_tx(&s.bar, kRowTileBytes);
+        bulk_g2s(s.twA, p.rtw + (size_t)mi * p.N + (size_t)blockIdx.x * (kRowTileBytes / 16), kRowTileBytes, &s.bar);
+    }
+    const B200Mod m = p.mods[mi];
+    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(blockIdx.x * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
 #pragma unroll
     for (int e = 0; e < 16; e++) v[e] = rowp[e * 16 + cl];
-    ct_phase<4, BIG>(v, tw, P, m);
+    __syncthreads();                     // barrier initialised before anyone polls it
+    mbar_wait(&s.bar, 0);
+    ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m);
+    // exchange: thread cl holds positions e*16+cl, wants cl*16+e
+    unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + rl * (kRowLen * 8);
+    {
+        const u32 b0 = cl * 8;
 #pragma unroll
-    for (int e = 0; e < 16; e++) sm[rl * kRowLen + swz(e * 16 + cl)] = v[e];
-    __syncthreads();
+        for (int e = 0; e < 16; e++) *reinterpret_cast<u64*>(xrow + e * 128 + (b0 ^ ((e & 7) << 4))) = v[e];
+    }
+    __syncwarp();                        // a row lives inside one half-warp
+    {
+        const u32 a0 = cl * 128 + ((cl & 7) << 4);
 #pragma unroll
-    for (int e = 0; e < 16; e++) v[e] = sm[rl * kRowLen + swz(cl * 16 + e)];
-    ct_phase<4, BIG>(v, tw, (P << 4) + cl, m);
+        for (int c = 0; c < 8; c++) {
+            const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(xrow + (a0 ^ (c << 4)));
+            v[2 * c] = t.x;
+            v[2 * c + 1] = t.y;
+        }
+    }
+    ct_phase<4, BIG>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m);
 #pragma unroll
-    for (int e = 0; e < 16; e++) v[e] = canon3(reduce_lazy<BIG>(v[e], m), m.q);
+    for (int e = 0; e < 16; e++) v[e] = BIG ? canon2(reduce_lazy<BIG>(v[e], m), m.q) : canon3(reduce_lazy<BIG>(v[e], m), m.q);
     ulonglong2* out = reinterpret_cast<ulonglong2*>(rowp + cl * 16);
 #pragma unroll
     for (int e = 0; e < 8; e++) out[e] = make_ulonglong2(v[2 * e], v[2 * e + 1]);
 }
 
-// ---------------------------------------------------------------- inverse, rows
 template <bool BIG>
-__global__ void __launch_bounds__(256) k_inv_row(PassArgs p) {
-    __shared__ u64 sm[kTile * kRowLen];
+__global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs p) {
+    extern __shared__ __align__(128) unsigned char smraw[];
+    RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
     const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
-    const B200Mod m = p.mods[mi];
-    const ulonglong2* itw = p.tw + (size_t)mi * p.N;
     const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
-    const u32 row = blockIdx.x * kTile + rl;
-    const u32 P = (p.N >> kRowLog) + row;
-    u64* rowp = p.data + (size_t)limb * p.N + (size_t)row * kRowLen;
+    if (threadIdx.x == 0) {
+        mbar_init(&s.bar, 1);
+        mbar_expect_tx(&s.bar, kRowTileBytes);
+        bulk_g2s(s.twA, p.rtw + (size_t)mi * p.N + (size_t)blockIdx.x * (kRowTileBytes / 16), kRowTileBytes, &s.bar);
+    }
+    const B200Mod m = p.mods[mi];
+    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(blockIdx.x * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
     const ulonglong2* in = reinterpret_cast<const ulonglong2*>(rowp + cl * 16);
 #pragma unroll
     for (int e = 0; e < 8; e++) { ulonglong2 x = in[e]; v[2 * e] = x.x; v[2 * e + 1] = x.y; }
-    gs_phase<4, BIG, false>(v, itw, (P << 4) + cl, m);
-#pragma unroll
-    for (int e = 0; e < 16; e++) sm[rl * kRowLen + swz(cl * 16 + e)] = v[e];
     __syncthreads();
+    mbar_wait(&s.bar, 0);
+    gs_phase<4, BIG, false>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m);
+    unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + rl * (kRowLen * 8);
+    {
+        const u32 a0 = cl * 128 + ((cl & 7) << 4);
 #pragma unroll
-    for (int e = 0; e < 16; e++) v[e] = sm[rl * kRowLen + swz(e * 16 + cl)];
-    gs_phase<4, BIG, false>(v, itw, P, m);
+        for (int c = 0; c < 8; c++)
+            *reinterpret_cast<ulonglong2*>(xrow + (a0 ^ (c << 4))) = make_ulonglong2(v[2 * c], v[2 * c + 1]);
+    }
+    __syncwarp();
+    {
+        const u32 b0 = cl * 8;
+#pragma unroll
+        for (int e = 0; e < 16; e++) v[e] = *reinterpret_cast<const u64*>(xrow + e * 128 + (b0 ^ ((e & 7) << 4)));
+    }
+    gs_phase<4, BIG, false>(v, TwList<1>{s.twA + rl * 16}, m);
 #pragma unroll
     for (int e = 0; e < 16; e++) rowp[e * 16 + cl] = v[e];
 }
@@ -131,7 +202,7 @@ k_inv_col(PassArgs p) {
             u64 w[RB];
 #pragma unroll
             for (int e = 0; e < RB; e++) w[e] = base[(size_t)(g * RB + e) * kRowLen + c];
-            gs_phase<LB, BIG, false>(w, itw, (1u << LA) + g, m);
+            gs_phase<LB, BIG, false>(w, TwGlobal{itw, (1u << LA) + g}, m);
 #pragma unroll
             for (int e = 0; e < RB; e++) sm[(g * RB + e) * kTile + c] = w[e];
         }
@@ -146,7 +217,7 @@ k_inv_col(PassArgs p) {
 #pragma unroll
             for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
         }
-        gs_phase<LA, BIG, true>(v, itw, 1u, m);
+        gs_phase<LA, BIG, true>(v, TwGlobal{itw, 1u}, m);
 #pragma unroll
         for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
     }
@@ -171,7 +242,7 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
             for (u32 b = threadIdx.x; b < N / 2; b += blockDim.x) {
                 const u32 i = b / t, j = b % t, x = 2 * i * t + j;
                 const ulonglong2 W = tw[mm + i];
-                const u64 X = a[x], T = canon2(shoup_mul(a[x + t], W.x, W.y, m.q), m.q);
+                const u64 X = a[x], T = canon2(shoup_mul(a[x + t], W.x, W.y, 0 - m.q), m.q);
                 a[x] = canon2(X + T, m.q);
                 a[x + t] = canon2(X + m.q - T, m.q);
             }
@@ -185,11 +256,11 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
                 const ulonglong2 W = tw[mm + i];
                 const u64 U = a[x], V = a[x + t];
                 a[x] = canon2(U + V, m.q);
-                a[x + t] = canon2(shoup_mul(U + m.q - V, W.x, W.y, m.q), m.q);
+                a[x + t] = canon2(shoup_mul(U + m.q - V, W.x, W.y, 0 - m.q), m.q);
             }
             __syncthreads();
         }
-        for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon2(shoup_mul(a[i], m.ninv, m.ninv_s, m.q), m.q);
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon2(shoup_mul(a[i], m.ninv, m.ninv_s, 0 - m.q), m.q);
         __syncthreads();
     }
     for (u32 i = threadIdx.x; i < N; i += blockDim.x) base[i] = a[i];
@@ -199,17 +270,23 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
 template <int LC, int LA, bool BIG>
 static void launch_fwd2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
-    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kTile, n_limbs);
+    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kRowsPerCta, n_limbs);
     constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (mask & 1) k_fwd_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
-    if (mask & 2) k_fwd_row<BIG><<<gr, 256, 0, s>>>(a);
+    if (mask & 2) {
+        cudaFuncSetAttribute(k_fwd_row<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
+        k_fwd_row<BIG><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
+    }
 }
 template <int LC, int LA, bool BIG>
 static void launch_inv2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
-    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kTile, n_limbs);
-    if (mask & 1) k_inv_row<BIG><<<gr, 256, 0, s>>>(a);
+    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kRowsPerCta, n_limbs);
+    if (mask & 1) {
+        cudaFuncSetAttribute(k_inv_row<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
+        k_inv_row<BIG><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
+    }
     constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_inv_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (mask & 2) k_inv_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);

@@ -10,16 +10,32 @@
 //     tw[(Pp << t) + g],   Pp = (P << k0) + x_hi
 // i.e. the same rule with P replaced by Pp.  The inverse (Gentleman-Sande)
 // walks the same indices backwards with the inverse table.
+//
+// A phase fetches its twiddles through a small functor so the same butterfly
+// code runs from the SEAL-layout table in global memory (column passes) and
+// from the TMA-staged shared-memory tile of the row passes.
 #pragma once
 #include "modarith.cuh"
 
+// tw[(Pp << t) + g] from the SEAL-layout (bit-reversed) table in global memory
+struct TwGlobal {
+    const ulonglong2* __restrict__ tw;
+    u32 Pp;
+    __device__ __forceinline__ ulonglong2 get(int t, int g) const { return __ldg(tw + ((Pp << t) + g)); }
+};
+// entry j = (1 << t) - 1 + g of a per-thread (or per-row) list with a fixed stride (shared memory)
+template <int STRIDE>
+struct TwList {
+    const ulonglong2* base;
+    __device__ __forceinline__ ulonglong2 get(int t, int g) const { return base[((1 << t) - 1 + g) * STRIDE]; }
+};
+
 // Forward Cooley-Tukey phase.  In: any 64-bit words (congruent to the wanted
-// residues).  Out: values < (3 + 2*LR) q  (<= 13q for LR = 5).
-template <int LR, bool BIG>
-__device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const ulonglong2* __restrict__ tw, u32 Pp,
-                                         const B200Mod& m) {
+// residues).  Out: values < (B0 + 2*LR) q, B0 = reduce_lazy's bound.
+template <int LR, bool BIG, class TW>
+__device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m) {
     constexpr int R = 1 << LR;
-    const u64 q = m.q, two_q = q << 1;
+    const u64 q = m.q, two_q = q << 1, nq = 0 - q;
 #pragma unroll
     for (int e = 0; e < R / 2; e++) v[e] = reduce_lazy<BIG>(v[e], m);   // X half of sub-stage 0
 #pragma unroll
@@ -27,11 +43,11 @@ __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const ulonglong2* __
         const int half = R >> (t + 1);
 #pragma unroll
         for (int g = 0; g < (1 << t); g++) {
-            const ulonglong2 W = ldg_tw(tw + ((Pp << t) + g));
+            const ulonglong2 W = tw.get(t, g);
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int a = g * 2 * half + i, b = a + half;
-                const u64 T = shoup_mul(v[b], W.x, W.y, q);
+                const u64 T = shoup_mul(v[b], W.x, W.y, nq);
                 const u64 X = v[a];
                 v[a] = X + T;
                 v[b] = X - T + two_q;
@@ -40,17 +56,16 @@ __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const ulonglong2* __
     }
 }
 
-// Inverse Gentleman-Sande phase.  In: any 64-bit words.  Out: values < 12q
-// (LR even) / < 6q (LR odd) unless LAST, in which case the final sub-stage
-// (global stage 0) folds N^-1 in and the outputs are canonical [0,q).
-template <int LR, bool BIG, bool LAST>
-__device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const ulonglong2* __restrict__ itw, u32 Pp,
-                                         const B200Mod& m) {
+// Inverse Gentleman-Sande phase.  In: any 64-bit words.  Out: lazily reduced
+// values (< 16q) unless LAST, in which case the final sub-stage (global stage 0)
+// folds N^-1 in and the outputs are canonical [0,q).
+template <int LR, bool BIG, bool LAST, class TW>
+__device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m) {
     constexpr int R = 1 << LR;
-    const u64 q = m.q;
+    const u64 q = m.q, nq = 0 - q;
 #pragma unroll
-    for (int e = 0; e < R; e++) v[e] = reduce_lazy<BIG>(v[e], m);       // all < 3q
-    int bound = 3;                                                      // compile-time after unroll
+    for (int e = 0; e < R; e++) v[e] = reduce_lazy<BIG>(v[e], m);
+    int bound = LazyBound<BIG>::value;                                  // compile-time after unroll
 #pragma unroll
     for (int n = 0; n < LR; n++) {
         const int t = LR - 1 - n;
@@ -60,7 +75,7 @@ __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const ulonglong2* __
 #pragma unroll
             for (int e = 0; e < R; e++)
                 if ((e & phalf) == 0) v[e] = reduce_lazy<BIG>(v[e], m);
-            bound = 3;
+            bound = LazyBound<BIG>::value;
         }
         const u64 bq = q * (u64)bound;
         const bool fold = LAST && (t == 0);
@@ -68,14 +83,14 @@ __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const ulonglong2* __
         for (int g = 0; g < (1 << t); g++) {
             ulonglong2 W;
             if (fold) { W.x = m.iw1n; W.y = m.iw1n_s; }
-            else W = ldg_tw(itw + ((Pp << t) + g));
+            else W = tw.get(t, g);
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int a = g * 2 * half + i, b = a + half;
                 const u64 U = v[a], V = v[b];
                 const u64 S = U + V;
-                v[b] = shoup_mul(U - V + bq, W.x, W.y, q);
-                v[a] = fold ? shoup_mul(S, m.ninv, m.ninv_s, q) : S;
+                v[b] = shoup_mul(U - V + bq, W.x, W.y, nq);
+                v[a] = fold ? shoup_mul(S, m.ninv, m.ninv_s, nq) : S;
             }
         }
         bound *= 2;

@@ -74,7 +74,9 @@ __device__ __forceinline__ u64 smul(u64 y, u64 w, u64 ws, u64 q, u64 nq) {
 
 #define ITERS 64
 template <int V>
-__global__ void __launch_bounds__(256) k(u64* out, u64 q, u64 wseed, long long* cyc) {
+__global__ void __launch_bounds__(1024) k(u64* out, u64 q, u64 wseed, long long* cyc, int* smhist) {
+    extern __shared__ u64 dummy_smem[];
+    if (threadIdx.x == 0) { u32 sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); atomicAdd(&smhist[sm], 1); }
     u64 v[16];
     const u64 nq = 0 - q, two_q = 2 * q;
     u64 w[4], ws[4];
@@ -122,13 +124,20 @@ void run(const char* name) {
     cudaMalloc(&out, 148 * 1024 * 8 * 2);
     cudaMallocManaged(&cyc, 8);
     const u64 q = 1152921504606584833ull;
-    for (int threads = 128; threads <= 1024; threads *= 2) {
+    int* hist;
+    cudaMallocManaged(&hist, 256 * 4);
+    cudaFuncSetAttribute(k<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    for (int threads = 128; threads <= 1024; threads += (threads < 256 ? 128 : 256)) {
+        int mx = 0;
         for (int rep = 0; rep < 2; rep++) {
             *cyc = 0;
-            if (threads <= 256) k<V><<<148, threads>>>(out, q, 0x9E3779B97F4A7C15ull, cyc);
-            else k<V><<<148 * (threads / 256), 256>>>(out, q, 0x9E3779B97F4A7C15ull, cyc);
+            for (int i = 0; i < 256; i++) hist[i] = 0;
+            k<V><<<148, threads, 120 * 1024>>>(out, q, 0x9E3779B97F4A7C15ull, cyc, hist);
             cudaDeviceSynchronize();
+            mx = 0;
+            for (int i = 0; i < 256; i++) mx = hist[i] > mx ? hist[i] : mx;
         }
+        if (mx != 1) printf("  (max CTAs on one SM = %d)\n", mx);
         double warp_bf_per_smsp = (double)ITERS * 32 * (threads / 32) / 4.0;
         printf("%-34s warps/SM=%2d  cycles=%8lld  cyc/warp-butterfly/SMSP=%.2f\n", name, threads / 32, *cyc,
                *cyc / warp_bf_per_smsp);

@@ -6,11 +6,12 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
-#define ITERS 512
+#define ITERS 256
 #define CHAINS 8
 
 template <int OP>
-__global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed, long long* cyc) {
+__global__ void __launch_bounds__(1024) k(uint32_t* out, uint32_t seed, long long* cyc) {
+    extern __shared__ uint32_t dummy_smem[];
     uint32_t a[CHAINS], b[CHAINS];
     uint64_t w[CHAINS];
     double d[CHAINS];
@@ -22,7 +23,7 @@ __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed, long long
         d[i] = (double)a[i];
     }
     long long t0 = clock64();
-#pragma unroll 1
+#pragma unroll 4
     for (int it = 0; it < ITERS; it++) {
 #pragma unroll
         for (int i = 0; i < CHAINS; i++) {
@@ -51,22 +52,22 @@ __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed, long long
 #pragma unroll
     for (int i = 0; i < CHAINS; i++) acc ^= a[i] ^ b[i] ^ (uint32_t)w[i] ^ (uint32_t)(w[i] >> 32) ^ (uint32_t)d[i];
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
-    if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
+    if (threadIdx.x == 0) atomicMax((unsigned long long*)cyc, (unsigned long long)(t1 - t0));
 }
 
 template <int OP>
 void run(const char* name, int per_iter) {
     uint32_t* out;
     long long* cyc;
-    cudaMalloc(&out, 148 * 8 * 256 * 4);
+    cudaMalloc(&out, 148 * 1024 * 4);
     cudaMallocManaged(&cyc, 8);
-    for (int warps = 4; warps <= 32; warps *= 2) {   // warps per SM (1 CTA/SM of warps*32 threads... use 256-thread CTAs)
-        int ctas = 148 * (warps * 32 / 256 ? warps * 32 / 256 : 1);
-        int threads = warps * 32 < 256 ? warps * 32 : 256;
-        k<OP><<<ctas, threads>>>(out, 12345, cyc);
-        cudaDeviceSynchronize();
-        k<OP><<<ctas, threads>>>(out, 12345, cyc);
-        cudaDeviceSynchronize();
+    cudaFuncSetAttribute(k<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    for (int warps = 8; warps <= 32; warps *= 2) {   // 1 CTA per SM (120 KB smem), CTA = warps*32 threads
+        for (int rep = 0; rep < 3; rep++) {
+            *cyc = 0;
+            k<OP><<<148, warps * 32, 120 * 1024>>>(out, 12345, cyc);
+            cudaDeviceSynchronize();
+        }
         double warp_instr_per_smsp = (double)ITERS * CHAINS * per_iter * warps / 4.0;
         printf("%-28s warps/SM=%2d  cycles=%8lld  cyc/warp-instr/SMSP=%.2f\n", name, warps, *cyc, *cyc / warp_instr_per_smsp);
     }
