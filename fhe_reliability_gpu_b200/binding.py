@@ -34,6 +34,8 @@ SIGNATURES = {
     "b200fhe_nwt_backward": (i32, [vp, vp, sz, sz, sz, vp]),
     "b200fhe_nwt_forward_host": (i32, [vp, U64P, sz, sz, sz]),
     "b200fhe_nwt_backward_host": (i32, [vp, U64P, sz, sz, sz]),
+    "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
+    "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
     "b200fhe_host_alloc": (i32, [C.POINTER(vp), sz]),
     "b200fhe_host_free": (i32, [vp]),
@@ -131,6 +133,29 @@ class Context:
 
     def nwt_backward_host(self, a, L=None, start_mod=0):
         return self._host(lib().b200fhe_nwt_backward_host, a, L, start_mod)
+
+
+def _pmult_accum_host(self, ct, pt, L=None, start_mod=0):
+    """ct [T][P][L][N], pt [T][L][N] (numpy uint64) -> out [P][L][N] = sum_k ct_k * pt_k mod q."""
+    L = self.L if L is None else L
+    ct = np.ascontiguousarray(ct, dtype=np.uint64); pt = np.ascontiguousarray(pt, dtype=np.uint64)
+    T, P = ct.shape[0], ct.shape[1]
+    assert ct.shape == (T, P, L, self.N) and pt.shape == (T, L, self.N)
+    out = np.zeros((P, L, self.N), dtype=np.uint64)
+    check(lib().b200fhe_pmult_accum_host(self._h, _p(ct), _p(pt), T, _p(out), P, L, start_mod))
+    return out
+
+
+def _pmult_accum(self, ct_ptrs, pt_ptrs, out_ptr, n_poly, L=None, start_mod=0, accumulate=False, stream=0):
+    """device pointers (ints): ct_ptrs[k] -> [P][L][N], pt_ptrs[k] -> [L][N], out_ptr -> [P][L][N]."""
+    T = len(ct_ptrs)
+    a = (vp * max(T, 1))(*ct_ptrs); b = (vp * max(T, 1))(*pt_ptrs)
+    check(lib().b200fhe_pmult_accum(self._h, a, b, T, out_ptr, n_poly, self.L if L is None else L, start_mod,
+                                    1 if accumulate else 0, stream))
+
+
+Context.pmult_accum_host = _pmult_accum_host
+Context.pmult_accum = _pmult_accum
 
 
 def flip_bit(ptr, idx, bit, stream=0):

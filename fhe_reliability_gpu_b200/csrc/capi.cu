@@ -367,6 +367,82 @@ extern "C" int b200fhe_nwt_backward_host(b200fhe_ctx* c, uint64_t* h, size_t n_p
     return run_ntt_host(c, true, h, n_poly, L, start);
 }
 
+// ---------------------------------------------------------------- pmult
+static int check_limbs(const b200fhe_ctx* c, size_t L, size_t start, const char* what) {
+    if (!c) return b200_set_err(B200FHE_EINVAL, "%s: null ctx", what);
+    if (start + L > (size_t)c->L) return b200_set_err(B200FHE_EINVAL, "%s: start_mod %zu + L %zu exceeds context (%d)", what, start, L, c->L);
+    for (size_t i = start; i < start + L; i++)
+        if (!c->moduli[i]) return b200_set_err(B200FHE_EINVAL, "%s: modulus %zu not set", what, i);
+    return 0;
+}
+
+extern "C" int b200fhe_pmult_accum(b200fhe_ctx* c, const uint64_t* const* ct, const uint64_t* const* pt, size_t T, uint64_t* d_out,
+                                   size_t P, size_t L, size_t start, int accumulate, void* stream) {
+    int rc = check_limbs(c, L, start, "pmult");
+    if (rc) return rc;
+    if (P == 0 || L == 0) return 0;
+    if (!d_out || (T && (!ct || !pt))) return b200_set_err(B200FHE_EINVAL, "pmult: null argument");
+    for (size_t k = 0; k < T; k++)
+        if (!ct[k] || !pt[k]) return b200_set_err(B200FHE_EINVAL, "pmult: null term %zu", k);
+    CK(cudaSetDevice(c->device));
+    rc = launch_pmult((const u64* const*)ct, (const u64* const*)pt, T, (u64*)d_out, c->d_mods, (u32)c->N, (u32)P, (u32)L, (u32)start,
+                      accumulate, (cudaStream_t)stream, &g_launches);
+    if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "pmult: N=%zu unsupported", c->N);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200fhe_pmult_accum_host(b200fhe_ctx* c, const uint64_t* h_ct, const uint64_t* h_pt, size_t T, uint64_t* h_out, size_t P,
+                                        size_t L, size_t start) {
+    int rc = check_limbs(c, L, start, "pmult_host");
+    if (rc) return rc;
+    if (P == 0 || L == 0) return 0;
+    if (!h_out || (T && (!h_ct || !h_pt))) return b200_set_err(B200FHE_EINVAL, "pmult_host: null argument");
+    CK(cudaSetDevice(c->device));
+    const size_t ptw = L * c->N, ctw = P * ptw;
+    // chunk of terms per buffer: about 256 MiB of input, two buffers in flight
+    size_t tc = ((size_t)256 << 20) / ((ctw + ptw) * sizeof(uint64_t));
+    if (tc < 1) tc = 1;
+    if (tc > 64) tc = 64;
+    if (T && tc > T) tc = T;
+    const size_t bufw = tc * (ctw + ptw);
+    rc = b200_ensure_stage(c, 2 * bufw + ctw, false);
+    if (rc) return rc;
+    if (!c->s_h2d) {
+        CK(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+    }
+    if (c->ev.size() < 4) {
+        size_t old = c->ev.size();
+        c->ev.resize(4);
+        for (size_t i = old; i < 4; i++) CK(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
+    }
+    uint64_t* d_out = c->d_stage + 2 * bufw;
+    cudaStream_t sk = c->own_stream;
+    std::vector<const uint64_t*> pc(tc), pp(tc);
+    if (T == 0) {
+        rc = b200fhe_pmult_accum(c, nullptr, nullptr, 0, d_out, P, L, start, 0, sk);
+        if (rc) return rc;
+    }
+    size_t chunk = 0;
+    for (size_t k0 = 0; k0 < T; k0 += tc, chunk++) {
+        const size_t n = T - k0 < tc ? T - k0 : tc;
+        uint64_t* buf = c->d_stage + (chunk & 1) * bufw;
+        if (chunk >= 2) CK(cudaStreamWaitEvent(c->s_h2d, c->ev[2 + (chunk & 1)], 0));   // kernel that last read this buffer
+        CK(cudaMemcpyAsync(buf, h_ct + k0 * ctw, n * ctw * sizeof(uint64_t), cudaMemcpyHostToDevice, c->s_h2d));
+        CK(cudaMemcpyAsync(buf + tc * ctw, h_pt + k0 * ptw, n * ptw * sizeof(uint64_t), cudaMemcpyHostToDevice, c->s_h2d));
+        CK(cudaEventRecord(c->ev[chunk & 1], c->s_h2d));
+        CK(cudaStreamWaitEvent(sk, c->ev[chunk & 1], 0));
+        for (size_t k = 0; k < n; k++) { pc[k] = buf + k * ctw; pp[k] = buf + tc * ctw + k * ptw; }
+        rc = b200fhe_pmult_accum(c, pc.data(), pp.data(), n, d_out, P, L, start, k0 != 0, sk);
+        if (rc) return rc;
+        CK(cudaEventRecord(c->ev[2 + (chunk & 1)], sk));
+    }
+    CK(cudaMemcpyAsync(h_out, d_out, ctw * sizeof(uint64_t), cudaMemcpyDeviceToHost, sk));
+    CK(cudaStreamSynchronize(sk));
+    return 0;
+}
+
 // ---------------------------------------------------------------- fault injection
 __global__ void k_flip_bit(u64* data, size_t idx, unsigned bit) { data[idx] ^= (1ull << bit); }
 

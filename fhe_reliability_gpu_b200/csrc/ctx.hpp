@@ -33,6 +33,10 @@ struct PassArgs {
 // mask: 1 = first pass only, 2 = second pass only, 3 = whole transform
 int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s);
 
+// ct[k] -> [P][L][N], pt[k] -> [L][N] (host arrays of T device pointers), out [P][L][N]
+int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
+                 u32 start_mod, int accumulate, cudaStream_t s, unsigned long long* launches);
+
 }  // namespace b200
 
 struct b200fhe_ctx {

@@ -1,0 +1,106 @@
+// RNS ciphertext x plaintext multiply-accumulate in the NTT domain (config C3):
+//   out[p][l][i] = sum_{k < T} ct_k[p][l][i] * pt_k[l][i]  mod q_l
+// Experiment definition: lattigo-error-demo/seal_pmult.cpp:52 (multiply_plain),
+// accumulate pattern profile_framewk/src/matmul_ckks.cpp:90-107, SEAL kernel
+// dyadic_product_coeffmod; GPU call site of the ct x ct flavour
+// reliability_test/dotprod_test.cu:113.
+//
+// Pure streaming kernel, HBM-bound: every ct word is read once, every pt word
+// once per call (shared by the P polynomials of a ciphertext inside the thread),
+// products are accumulated lazily in 192 bits and reduced ONCE per output
+// coefficient (two 128-bit Barrett steps), so arbitrary 64-bit input words
+// (bit-flipped residues, dotprod_test.cu:38-61) are handled exactly: the result
+// equals sum (ct mod q)(pt mod q) mod q.
+#include "ctx.hpp"
+
+namespace b200 {
+
+constexpr int kPmultTerms = 64;   // terms per launch (pointer table in kernel parameters)
+struct PmultPtrs {
+    const u64* ct[kPmultTerms];   // each [P][L][N]
+    const u64* pt[kPmultTerms];   // each [L][N]
+};
+
+struct Acc192 {
+    u64 a0, a1, a2;
+};
+__device__ __forceinline__ void acc_mad(Acc192& A, u64 x, u64 y) {
+    const u64 lo = x * y, hi = __umul64hi(x, y);
+    asm("add.cc.u64 %0, %0, %3;\n\taddc.cc.u64 %1, %1, %4;\n\taddc.u64 %2, %2, 0;"
+        : "+l"(A.a0), "+l"(A.a1), "+l"(A.a2)
+        : "l"(lo), "l"(hi));
+}
+// (a2:a1:a0) mod q, any 192-bit value
+__device__ __forceinline__ u64 acc_reduce(const Acc192& A, const B200Mod& m) {
+    const u64 r1 = barrett128(A.a1, A.a2, m);        // (a2:a1) mod q  < q
+    return barrett128(A.a0, r1, m);                  // (r1:a0) < q 2^64
+}
+
+// one thread = two consecutive coefficients of one limb, all P polynomials
+template <int P>
+__global__ void __launch_bounds__(256) k_pmult(const __grid_constant__ PmultPtrs ptrs, int T, u64* out, const B200Mod* mods,
+                                               u32 N, u32 L, u32 start_mod, int accumulate) {
+    const u32 limb = blockIdx.y;
+    const B200Mod m = mods[start_mod + limb];
+    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // index of the coefficient pair
+    if (i2 * 2 >= N) return;
+    const size_t off = ((size_t)limb * N) / 2 + i2;                    // in ulonglong2 units inside one [L][N] block
+    const size_t poly2 = ((size_t)L * N) / 2;
+    Acc192 acc[P][2];
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        acc[p][0] = Acc192{0, 0, 0};
+        acc[p][1] = Acc192{0, 0, 0};
+    }
+    if (accumulate) {
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+            const ulonglong2 o = reinterpret_cast<const ulonglong2*>(out)[p * poly2 + off];
+            acc[p][0].a0 = o.x;
+            acc[p][1].a0 = o.y;
+        }
+    }
+#pragma unroll 2
+    for (int k = 0; k < T; k++) {
+        const ulonglong2 w = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.pt[k]) + off);
+        ulonglong2 c[P];
+#pragma unroll
+        for (int p = 0; p < P; p++) c[p] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.ct[k]) + p * poly2 + off);
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+            acc_mad(acc[p][0], c[p].x, w.x);
+            acc_mad(acc[p][1], c[p].y, w.y);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < P; p++)
+        reinterpret_cast<ulonglong2*>(out)[p * poly2 + off] = make_ulonglong2(acc_reduce(acc[p][0], m), acc_reduce(acc[p][1], m));
+}
+
+// ct[k]: T device pointers to [P][L][N]; pt[k]: T device pointers to [L][N]; out [P][L][N].
+int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
+                 u32 start_mod, int accumulate, cudaStream_t s, unsigned long long* launches) {
+    if (N < 2) return -1;
+    const u32 threads = 256, pairs = N / 2;
+    dim3 grid((pairs + threads - 1) / threads, L);
+    for (u32 p0 = 0; p0 < P;) {
+        const u32 pc = (P - p0 >= 2) ? 2 : 1;
+        const size_t poff = (size_t)p0 * L * N;
+        for (size_t k0 = 0; k0 < T || (T == 0 && k0 == 0); k0 += kPmultTerms) {
+            PmultPtrs ptrs;
+            const int tc = (int)((T - k0) < (size_t)kPmultTerms ? (T - k0) : kPmultTerms);
+            for (int k = 0; k < kPmultTerms; k++) {
+                ptrs.ct[k] = k < tc ? ct[k0 + k] + poff : nullptr;
+                ptrs.pt[k] = k < tc ? pt[k0 + k] : nullptr;
+            }
+            if (pc == 2) k_pmult<2><<<grid, threads, 0, s>>>(ptrs, tc, out + poff, mods, N, L, start_mod, accumulate || k0 != 0);
+            else k_pmult<1><<<grid, threads, 0, s>>>(ptrs, tc, out + poff, mods, N, L, start_mod, accumulate || k0 != 0);
+            if (launches) ++*launches;
+            if (T == 0) break;
+        }
+        p0 += pc;
+    }
+    return 0;
+}
+
+}  // namespace b200

@@ -105,6 +105,24 @@ int b200fhe_nwt_backward_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly
 int b200fhe_host_alloc(void** p, size_t bytes);
 int b200fhe_host_free(void* p);
 
+/* ---- ct x pt multiply-accumulate (config C3) ------------------------------- */
+
+/* out[p][l][i] = sum_{k<n_terms} ct_k[p][l][i] * pt_k[l][i] mod q_{start_mod+l}, NTT domain.
+ * Replaces the per-term multiply_plain + add_inplace loop of
+ * profile_framewk/src/matmul_ckks.cpp:90-107 / lattigo-error-demo/seal_pmult.cpp:52
+ * (SEAL dyadic_product_coeffmod) and Phantom's multiply_plain on the device
+ * layout of reliability_test/dotprod_test.cu:42-46 ([size][L][N] per ciphertext).
+ * ct / pt are HOST arrays of n_terms DEVICE pointers (ct_k -> [n_poly][L][N],
+ * pt_k -> [L][N]); d_out is [n_poly][L][N].  Input words are taken mod q.  If
+ * `accumulate` is non-zero the previous contents of d_out (in [0,q)) are added. */
+int b200fhe_pmult_accum(b200fhe_ctx* ctx, const uint64_t* const* ct, const uint64_t* const* pt, size_t n_terms,
+                        uint64_t* d_out, size_t n_poly, size_t L, size_t start_mod, int accumulate, void* stream);
+
+/* Same on HOST buffers: h_ct [n_terms][n_poly][L][N], h_pt [n_terms][L][N], h_out
+ * [n_poly][L][N]; terms are streamed through the device in double-buffered chunks. */
+int b200fhe_pmult_accum_host(b200fhe_ctx* ctx, const uint64_t* h_ct, const uint64_t* h_pt, size_t n_terms, uint64_t* h_out,
+                             size_t n_poly, size_t L, size_t start_mod);
+
 /* Measurement hooks (bench.py): one pass of the two-kernel transform
  * (pass 1 = first kernel, 2 = second), and the number of kernels this library
  * has launched in this process. */
