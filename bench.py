@@ -204,6 +204,28 @@ def main():
         a1.record(stream)
         torch.cuda.synchronize()
         kern[name] = a0.elapsed_time(a1) / reps
+    # ABFT overhead: forward transform of the batch, unprotected vs protected (fused checksum), same data
+    verdict = torch.zeros(npoly * L, dtype=torch.int32, device="cuda")
+    vp_ = verdict.data_ptr()
+    def fwd_plain():
+        pkg.binding.check(lib.b200fhe_nwt_forward(ctx._h, dp, npoly, L, 0, sp))
+    def fwd_prot():
+        pkg.binding.check(lib.b200fhe_nwt_forward_protected(ctx._h, dp, npoly, L, 0, vp_, None, None, 0, sp))
+    abft_ms = {}
+    for name, fn in (("forward", fwd_plain), ("forward_protected", fwd_prot)):
+        for _ in range(3):
+            fn()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(stream)
+        for _ in range(max(args.steps, 5)):
+            fn()
+        a1.record(stream)
+        torch.cuda.synchronize()
+        abft_ms[name] = a0.elapsed_time(a1) / max(args.steps, 5)
+    abft = {"forward_ms": abft_ms["forward"], "forward_protected_ms": abft_ms["forward_protected"],
+            "overhead_pct": 100.0 * (abft_ms["forward_protected"] / abft_ms["forward"] - 1.0),
+            "faults_flagged_clean_run": int(verdict.sum().item()),
+            "note": "t(protected)/t(unprotected)-1 on the same %d-limb batch; checksum fused into first load / last store" % (npoly * L)}
     peak, peak_src = peaks()
     dom = max(kern, key=kern.get)
     # one pass kernel = half of a limb-transform's 16 B/coeff (the pair shares the 1 MiB)
@@ -243,7 +265,7 @@ def main():
                "config": config, "clocks": clocks, "gpu_launches": launches,
                "e2e": {"value": e2e_val, "unit": "limb-transforms/s", "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir,
                        "steps": e2e_steps, "timer": "host perf_counter around synchronous C-ABI calls, max over ranks"},
-               "roofline": roof}
+               "roofline": roof, "abft": abft}
         if world == 1 and not args.no_cpu_baseline:
             v, ms, cores, sample = cpu_reference(10, 1)
             out["cpu_baseline"] = {"value": v, "unit": "limb-transforms/s", "cores": cores, "kind": "port", "sample": sample}

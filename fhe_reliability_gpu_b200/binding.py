@@ -34,6 +34,9 @@ SIGNATURES = {
     "b200fhe_nwt_backward": (i32, [vp, vp, sz, sz, sz, vp]),
     "b200fhe_nwt_forward_host": (i32, [vp, U64P, sz, sz, sz]),
     "b200fhe_nwt_backward_host": (i32, [vp, U64P, sz, sz, sz]),
+    "b200fhe_nwt_forward_protected": (i32, [vp, vp, sz, sz, sz, vp, vp, vp, sz, vp]),
+    "b200fhe_nwt_forward_protected_host": (i32, [vp, U64P, sz, sz, sz, C.POINTER(C.c_uint32), U64P, vp, sz]),
+    "b200fhe_abft_weights": (i32, [vp, i32, U64P, U64P]),
     "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
@@ -135,6 +138,44 @@ class Context:
         return self._host(lib().b200fhe_nwt_backward_host, a, L, start_mod)
 
 
+class Inject(C.Structure):
+    """b200fhe_inject: one fault in relia_ntt_sim.cpp's operation numbering."""
+    _fields_ = [("limb", C.c_uint32), ("stage", C.c_uint32), ("butterfly", C.c_uint64), ("kind", C.c_uint32),
+                ("reserved", C.c_uint32), ("payload", C.c_uint64)]
+
+
+SBF, DBF, MLF = "SBF", "DBF", "MLF"     # fault kinds of relia_ntt_sim.cpp:109-132
+
+
+def make_plan(entries):
+    """entries: iterable of (limb, stage, butterfly, kind, payload) with kind 1 (xor) or 2 (replace)."""
+    entries = list(entries)
+    arr = (Inject * max(len(entries), 1))()
+    for i, (limb, stage, bf, kind, payload) in enumerate(entries):
+        arr[i] = Inject(limb, stage, bf, kind, 0, payload)
+    return arr, len(entries)
+
+
+def _nwt_forward_protected_host(self, a, L=None, start_mod=0, plan=()):
+    """In-place protected forward NTT of a [n_poly][L][N]; returns (a, verdict[n_limbs], sums[n_limbs][2])."""
+    L = self.L if L is None else L
+    assert a.dtype == np.uint64 and a.flags.c_contiguous and a.size % (L * self.N) == 0
+    n_poly = a.size // (L * self.N)
+    verdict = np.zeros(n_poly * L, dtype=np.uint32)
+    sums = np.zeros((n_poly * L, 2), dtype=np.uint64)
+    arr, n = make_plan(plan)
+    check(lib().b200fhe_nwt_forward_protected_host(self._h, _p(a), n_poly, L, start_mod,
+                                                   verdict.ctypes.data_as(C.POINTER(C.c_uint32)), _p(sums),
+                                                   C.cast(arr, vp), n))
+    return a, verdict, sums
+
+
+def _abft_weights(self, idx):
+    w = np.zeros(self.N, dtype=np.uint64); wh = np.zeros(self.N, dtype=np.uint64)
+    check(lib().b200fhe_abft_weights(self._h, idx, _p(w), _p(wh)))
+    return w, wh
+
+
 def _pmult_accum_host(self, ct, pt, L=None, start_mod=0):
     """ct [T][P][L][N], pt [T][L][N] (numpy uint64) -> out [P][L][N] = sum_k ct_k * pt_k mod q."""
     L = self.L if L is None else L
@@ -154,6 +195,8 @@ def _pmult_accum(self, ct_ptrs, pt_ptrs, out_ptr, n_poly, L=None, start_mod=0, a
                                     1 if accumulate else 0, stream))
 
 
+Context.nwt_forward_protected_host = _nwt_forward_protected_host
+Context.abft_weights = _abft_weights
 Context.pmult_accum_host = _pmult_accum_host
 Context.pmult_accum = _pmult_accum
 

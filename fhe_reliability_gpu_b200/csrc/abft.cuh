@@ -1,0 +1,79 @@
+// Fused ABFT weighted checksum of the forward NTT (config C4).
+//
+// Identity (rfhe_framewk/src/negaclic_ntt.py:130-149 ecc_check):
+//     sum_i w_i a_i  ==  sum_k omega_k NTT(a)_k   (mod q),   omega = N^-1 NTT_{psi^-1}(w)
+// with the prototype's small weights w = generate_weights(N) (:8-13).  The left
+// side is accumulated while the FIRST pass loads the coefficients, the right
+// side while the LAST pass stores the results -- no extra pass over the data
+// (north_star: "checksum accumulation fused into the final stage").  A fault in
+// any butterfly in between breaks the identity unless its effect on the sum is a
+// multiple of q (miss probability ~ 1/q, as in relia_ntt_sim's batch checks).
+//
+// Cost control: every weighted product is carry-free.  w_i < 2^12, so
+// w_i * lo32(a) and w_i * hi32(a) are accumulated by two IMAD.WIDE into two
+// 64-bit sums; omega_k and the canonical outputs are split at 30 bits so the four
+// partial products of 16 coefficients fit 64-bit sums.  One Barrett reduction
+// partial products of 16 coefficients fit 64-bit sums.  The per-thread sums are committed
+// unreduced (20-bit digits, one REDUX + one atomic per digit per warp); the single modular
+// reduction per limb happens in k_abft_finalize.
+#pragma once
+#include "modarith.cuh"
+
+struct AbftIn {
+    u64 lo = 0, hi = 0;
+    __device__ __forceinline__ void add(u32 w, u64 x) {
+        u32 xl, xh;
+        unpack64(x, xl, xh);
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(lo) : "r"(w), "r"(xl));
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(hi) : "r"(w), "r"(xh));
+    }
+    // lo + hi 2^32 as a 128-bit number (< 2^92 for up to 32 terms of w < 2^12)
+    __device__ __forceinline__ void value(u64& s0, u64& s1) const {
+        s0 = lo + (hi << 32);
+        s1 = (hi >> 32) + (s0 < lo);
+    }
+};
+
+struct AbftOut {
+    u64 p00 = 0, p01 = 0, p10 = 0, p11 = 0;
+    // om = omega0 | omega1 << 32 (30-bit halves), x canonical (< 2^60)
+    __device__ __forceinline__ void add(u64 om, u64 x) {
+        u32 o0, o1;
+        unpack64(om, o0, o1);
+        const u32 x0 = (u32)x & 0x3fffffffu, x1 = (u32)(x >> 30);
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p00) : "r"(o0), "r"(x0));
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p01) : "r"(o0), "r"(x1));
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p10) : "r"(o1), "r"(x0));
+        asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p11) : "r"(o1), "r"(x1));
+    }
+    // p00 + (p01 + p10) 2^30 + p11 2^60  < 2^125
+    __device__ __forceinline__ void value(u64& s0, u64& s1) const {
+        u64 t;
+        s0 = p00; s1 = 0;
+        t = p01 << 30; s0 += t; s1 += (p01 >> 34) + (s0 < t);
+        t = p10 << 30; s0 += t; s1 += (p10 >> 34) + (s0 < t);
+        t = p11 << 60; s0 += t; s1 += (p11 >> 4) + (s0 < t);
+    }
+};
+
+// counters: [limb][side][8] u64, side 0 = input sum, 1 = output sum.  The 128-bit per-thread sum
+// (s1:s0) is committed unreduced as NDIG 20-bit digits: one REDUX per digit and one atomic per digit
+// per warp; k_abft_finalize recombines the digit sums and reduces mod q once per limb.
+constexpr int kAbftStride = 8;
+template <int NDIG>
+__device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u64 s0, u64 s1) {
+    u64* c = counters + ((size_t)limb * 2 + side) * kAbftStride;
+#pragma unroll
+    for (int d = 0; d < NDIG; d++) {
+        const int sh = 20 * d;
+        u32 dig;
+        if (sh + 20 <= 64) dig = (u32)(s0 >> sh) & 0xfffffu;
+        else if (sh >= 64) dig = (u32)(s1 >> (sh - 64)) & 0xfffffu;
+        else dig = (u32)((s0 >> sh) | (s1 << (64 - sh))) & 0xfffffu;
+        const u32 sum = __reduce_add_sync(0xffffffffu, dig);
+        if ((threadIdx.x & 31) == 0) atomicAdd(reinterpret_cast<unsigned long long*>(c + d), (unsigned long long)sum);
+    }
+}
+
+// generate_weights(N): w_i = (i mod p) + (i div p) + 2, p = 2^pl
+__device__ __forceinline__ u32 abft_w(u32 i, int pl) { return (i & ((1u << pl) - 1)) + (i >> pl) + 2; }

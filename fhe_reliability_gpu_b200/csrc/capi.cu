@@ -98,6 +98,7 @@ extern "C" int b200fhe_ctx_create_empty(int log_n, int L, int device, b200fhe_ct
     c->h_mods.resize(L);
     memset(c->h_mods.data(), 0, sizeof(B200Mod) * L);
     c->has_inverse.assign(L, 0);
+    c->has_omega.assign(L, 0);
     cudaError_t e = cudaMalloc(&c->d_mods, sizeof(B200Mod) * L);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_tw, sizeof(ulonglong2) * c->N * L);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_itw, sizeof(ulonglong2) * c->N * L);
@@ -169,6 +170,8 @@ extern "C" int b200fhe_ctx_set_tables(b200fhe_ctx* c, int idx, uint64_t q, const
         c->has_inverse[idx] = 0;
     }
     c->moduli[idx] = q;
+    c->psi[idx] = N > 1 ? tw[N >> 1] : 1;   // root_powers[bitrev(1)] = psi
+    c->has_omega[idx] = 0;
     c->h_mods[idx] = make_mod(q, c->log_n, itw1, n_inv);
     CK(cudaMemcpyAsync(c->d_mods + idx, &c->h_mods[idx], sizeof(B200Mod), cudaMemcpyHostToDevice, s));
     CK(cudaStreamSynchronize(s));
@@ -206,6 +209,9 @@ extern "C" int b200fhe_ctx_destroy(b200fhe_ctx* c) {
     if (c->d_itw) cudaFree(c->d_itw);
     if (c->d_rtw) cudaFree(c->d_rtw);
     if (c->d_irtw) cudaFree(c->d_irtw);
+    if (c->d_omega) cudaFree(c->d_omega);
+    if (c->d_abft) cudaFree(c->d_abft);
+    if (c->d_inj) cudaFree(c->d_inj);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -365,6 +371,115 @@ extern "C" int b200fhe_nwt_forward_host(b200fhe_ctx* c, uint64_t* h, size_t n_po
 }
 extern "C" int b200fhe_nwt_backward_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start) {
     return run_ntt_host(c, true, h, n_poly, L, start);
+}
+
+// ---------------------------------------------------------------- protected forward NTT
+static int check_limbs(const b200fhe_ctx* c, size_t L, size_t start, const char* what);
+static int ensure_abft(b200fhe_ctx* c, size_t start, size_t L, size_t n_limbs) {
+    if (!c->d_omega) CK(cudaMalloc(&c->d_omega, sizeof(uint64_t) * c->N * c->L));
+    if (!c->d_inj) CK(cudaMalloc(&c->d_inj, sizeof(InjEntry) * B200FHE_MAX_INJECT));
+    if (c->abft_limbs < n_limbs) {
+        if (c->d_abft) cudaFree(c->d_abft);
+        c->d_abft = nullptr; c->abft_limbs = 0;
+        CK(cudaMalloc(&c->d_abft, sizeof(uint64_t) * 16 * n_limbs));
+        CK(cudaMemset(c->d_abft, 0, sizeof(uint64_t) * 16 * n_limbs));
+        c->abft_limbs = n_limbs;
+    }
+    std::vector<uint64_t> om(c->N);
+    for (size_t i = start; i < start + L; i++) {
+        if (c->has_omega[i]) continue;
+        nt::abft_output_weights(c->log_n, c->moduli[i], c->psi[i], om.data());
+        for (size_t k = 0; k < c->N; k++) om[k] = (om[k] & 0x3fffffffull) | ((om[k] >> 30) << 32);   // 30-bit halves
+        CK(cudaMemcpy(c->d_omega + i * c->N, om.data(), sizeof(uint64_t) * c->N, cudaMemcpyHostToDevice));
+        c->has_omega[i] = 1;
+    }
+    return 0;
+}
+
+extern "C" int b200fhe_abft_weights(b200fhe_ctx* c, int idx, uint64_t* w, uint64_t* w_hat) {
+    if (!c || idx < 0 || idx >= c->L || !c->moduli[idx]) return b200_set_err(B200FHE_EINVAL, "abft_weights: bad modulus index");
+    if (w) for (size_t i = 0; i < c->N; i++) w[i] = nt::abft_input_weight(i, c->log_n);
+    if (w_hat) nt::abft_output_weights(c->log_n, c->moduli[idx], c->psi[idx], w_hat);
+    return 0;
+}
+
+extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, uint32_t* d_verdict,
+                                             uint64_t* d_sums, const b200fhe_inject* plan, size_t n_plan, void* stream) {
+    int rc = check_limbs(c, L, start, "nwt_protected");
+    if (rc) return rc;
+    if (n_poly == 0 || L == 0) return 0;
+    if (!d || !d_verdict) return b200_set_err(B200FHE_EINVAL, "nwt_protected: null argument");
+    if (n_plan > B200FHE_MAX_INJECT || (n_plan && !plan)) return b200_set_err(B200FHE_EINVAL, "nwt_protected: bad injection plan");
+    const size_t n_limbs = n_poly * L;
+    CK(cudaSetDevice(c->device));
+    rc = ensure_abft(c, start, L, n_limbs);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    InjEntry h[B200FHE_MAX_INJECT];
+    for (size_t i = 0; i < n_plan; i++) {
+        if (plan[i].limb >= n_limbs || plan[i].stage >= (uint32_t)c->log_n || plan[i].butterfly >= c->N / 2 || plan[i].kind < 1 || plan[i].kind > 2)
+            return b200_set_err(B200FHE_EINVAL, "nwt_protected: injection %zu out of range", i);
+        const uint64_t gap = c->N >> (plan[i].stage + 1);
+        h[i].limb = plan[i].limb;
+        h[i].stage = plan[i].stage;
+        h[i].xa = (u32)(2 * (plan[i].butterfly / gap) * gap + plan[i].butterfly % gap);
+        h[i].kind = plan[i].kind;
+        h[i].payload = plan[i].payload;
+    }
+    if (n_plan) CK(cudaMemcpyAsync(c->d_inj, h, sizeof(InjEntry) * n_plan, cudaMemcpyHostToDevice, s));
+    bool big = true;
+    for (size_t i = start; i < start + L; i++) big = big && c->h_mods[i].big;
+    PassArgs a;
+    a.mods = c->d_mods;
+    a.tw = c->d_tw;
+    a.rtw = c->d_rtw;
+    a.N = (u32)c->N;
+    a.L = (u32)L;
+    a.start_mod = (u32)start;
+    a.omega = (const u64*)c->d_omega;
+    a.abft = (u64*)c->d_abft;
+    a.inj = c->d_inj;
+    a.n_inj = (u32)n_plan;
+    size_t step = chunk_polys(c, L);
+    if (step * L > 32768) step = 32768 / L ? 32768 / L : 1;
+    for (size_t p0 = 0; p0 < n_poly; p0 += step) {
+        const size_t np = n_poly - p0 < step ? n_poly - p0 : step;
+        a.data = (u64*)d + p0 * L * c->N;
+        a.limb0 = (u32)(p0 * L);
+        rc = launch_ntt_protected(big, a, c->log_n, (u32)(np * L), s);
+        if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt_protected: log_n=%d unsupported (rc=%d)", c->log_n, rc);
+        g_launches += c->log_n <= 11 ? 1 : 2;
+    }
+    launch_abft_finalize((u64*)c->d_abft, c->d_mods, (u32)L, (u32)start, (u32)n_limbs, d_verdict, (u64*)d_sums, s);
+    g_launches += 1;
+    CK(cudaGetLastError());
+    if (n_plan) CK(cudaStreamSynchronize(s));   // h[] is a stack buffer
+    return 0;
+}
+
+extern "C" int b200fhe_nwt_forward_protected_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start, uint32_t* h_verdict,
+                                                  uint64_t* h_sums, const b200fhe_inject* plan, size_t n_plan) {
+    int rc = check_limbs(c, L, start, "nwt_protected_host");
+    if (rc) return rc;
+    if (n_poly == 0 || L == 0) return 0;
+    if (!h || !h_verdict) return b200_set_err(B200FHE_EINVAL, "nwt_protected_host: null argument");
+    CK(cudaSetDevice(c->device));
+    const size_t words = n_poly * L * c->N, n_limbs = n_poly * L;
+    // staging: data | sums [n_limbs][2] | verdict (u32, padded to words)
+    const size_t extra = 2 * n_limbs + (n_limbs + 1) / 2;
+    rc = b200_ensure_stage(c, words + extra, false);
+    if (rc) return rc;
+    uint64_t* d_sums = c->d_stage + words;
+    uint32_t* d_verdict = reinterpret_cast<uint32_t*>(d_sums + 2 * n_limbs);
+    cudaStream_t s = c->own_stream;
+    CK(cudaMemcpyAsync(c->d_stage, h, words * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+    rc = b200fhe_nwt_forward_protected(c, c->d_stage, n_poly, L, start, d_verdict, d_sums, plan, n_plan, s);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h, c->d_stage, words * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h_verdict, d_verdict, n_limbs * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    if (h_sums) CK(cudaMemcpyAsync(h_sums, d_sums, 2 * n_limbs * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
 }
 
 // ---------------------------------------------------------------- pmult

@@ -10,6 +10,7 @@
 #include <vector>
 #include <cuda_runtime.h>
 #include "modarith.cuh"
+#include "ntt_phases.cuh"
 
 namespace b200 {
 
@@ -28,10 +29,20 @@ struct PassArgs {
     u32 N;
     u32 L;                    // limbs per polynomial in this call
     u32 start_mod;
+    // protected (ABFT) forward transform only
+    const u64* omega = nullptr;     // [ctx.L][N] output weights, 30-bit halves packed (lo | hi << 32)
+    u64* abft = nullptr;            // [n_limbs of the call][2][4] digit-sum counters
+    const InjEntry* inj = nullptr;  // device copy of the injection plan
+    u32 n_inj = 0;
+    u32 limb0 = 0;                  // call-level index of this launch's first limb
 };
 
 // mask: 1 = first pass only, 2 = second pass only, 3 = whole transform
 int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s);
+// protected forward transform (a.omega / a.abft set); counters must be zero on entry
+int launch_ntt_protected(bool big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s);
+// verdict[i] = (input checksum != output checksum); sums (optional) [n][2]; zeroes the counters
+void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s);
 
 // ct[k] -> [P][L][N], pt[k] -> [L][N] (host arrays of T device pointers), out [P][L][N]
 int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
@@ -53,6 +64,12 @@ struct b200fhe_ctx {
     ulonglong2* d_itw = nullptr;     // [L][N] inverse
     ulonglong2* d_rtw = nullptr;     // [L][N] forward, row-pass tiles (N >= 2^12)
     ulonglong2* d_irtw = nullptr;    // [L][N] inverse, row-pass tiles
+    // ABFT (built lazily by the first protected call)
+    uint64_t* d_omega = nullptr;     // [L][N]
+    std::vector<uint8_t> has_omega;  // per modulus
+    uint64_t* d_abft = nullptr;      // counters, grown on demand
+    size_t abft_limbs = 0;
+    InjEntry* d_inj = nullptr;       // injection plan staging (kMaxInject entries)
     // host-buffer entry points: pinned staging + device scratch, grown on demand
     uint64_t* h_stage = nullptr;
     uint64_t* d_stage = nullptr;

@@ -14,6 +14,7 @@
 // Intermediates are stored lazily (< 16q); only final outputs are canonical.
 #include "ntt_phases.cuh"
 #include "ctx.hpp"
+#include "abft.cuh"
 
 namespace b200 {
 
@@ -51,7 +52,9 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 }
 
 // ---------------------------------------------------------------- forward, columns
-template <int LC, int LA, bool BIG>
+// PROT: the protected transform (config C4) -- accumulates the input side of the
+// ABFT checksum while the coefficients are loaded and honours the injection plan.
+template <int LC, int LA, bool BIG, bool PROT, bool INJ>
 __global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
 k_fwd_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
@@ -61,11 +64,24 @@ k_fwd_col(PassArgs p) {
     const ulonglong2* tw = p.tw + (size_t)mi * p.N;
     u64* base = p.data + (size_t)limb * p.N + blockIdx.x * kTile;
     const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
+    const u32 col = blockIdx.x * kTile + c;
+    u64 ck0 = 0, ck1 = 0;
     if (g < RB) {
         u64 v[RA];
 #pragma unroll
         for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
-        ct_phase<LA, BIG>(v, TwGlobal{tw, 1u}, m);
+        if constexpr (PROT) {
+            AbftIn acc;
+            const int pl = (LC + kRowLog + 1) / 2;
+#pragma unroll
+            for (int e = 0; e < RA; e++) acc.add(abft_w((u32)(e * RB + g) * kRowLen + col, pl), v[e]);
+            acc.value(ck0, ck1);
+        }
+        if constexpr (INJ)
+            ct_phase<LA, BIG>(v, TwGlobal{tw, 1u}, m,
+                              Inject{p.inj, p.n_inj, p.limb0 + limb, (u32)g * kRowLen + col, (u32)(LB + kRowLog), 0u, m.q});
+        else
+            ct_phase<LA, BIG>(v, TwGlobal{tw, 1u}, m);
         if (LB > 0) {
 #pragma unroll
             for (int e = 0; e < RA; e++) sm[(e * RB + g) * kTile + c] = v[e];
@@ -74,13 +90,18 @@ k_fwd_col(PassArgs p) {
             for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
         }
     }
+    if constexpr (PROT) abft_commit<5>(p.abft, p.limb0 + limb, 0, ck0, ck1);
     if constexpr (LB > 0) {
         __syncthreads();
         if (g < RA) {
             u64 w[RB];
 #pragma unroll
             for (int e = 0; e < RB; e++) w[e] = sm[(g * RB + e) * kTile + c];
-            ct_phase<LB, BIG>(w, TwGlobal{tw, (1u << LA) + g}, m);
+            if constexpr (INJ)
+                ct_phase<LB, BIG>(w, TwGlobal{tw, (1u << LA) + g}, m,
+                                  Inject{p.inj, p.n_inj, p.limb0 + limb, (u32)(g * RB) * kRowLen + col, (u32)kRowLog, (u32)LA, m.q});
+            else
+                ct_phase<LB, BIG>(w, TwGlobal{tw, (1u << LA) + g}, m);
 #pragma unroll
             for (int e = 0; e < RB; e++) base[(size_t)(g * RB + e) * kRowLen + c] = w[e];
         }
@@ -104,7 +125,7 @@ struct RowSmem {
 constexpr u32 kRowTileBytes = sizeof(ulonglong2) * kRowTileEntries;
 constexpr int kRowCtasPerSm = (220 * 1024) / (int)sizeof(RowSmem) > 16 ? 16 : (220 * 1024) / (int)sizeof(RowSmem);
 
-template <bool BIG>
+template <bool BIG, bool PROT, bool INJ>
 __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
     RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
@@ -122,7 +143,10 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
     for (int e = 0; e < 16; e++) v[e] = rowp[e * 16 + cl];
     __syncthreads();                     // barrier initialised before anyone polls it
     mbar_wait(&s.bar, 0);
-    ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m);
+    const u32 x0 = (blockIdx.x * kRowsPerCta + rl) * kRowLen;     // first coefficient of the row
+    const u32 lc = 31 - __clz(p.N >> kRowLog);                     // stages done by the column pass
+    if constexpr (INJ) ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m, Inject{p.inj, p.n_inj, p.limb0 + limb, x0 + cl, 4u, lc, m.q});
+    else ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m);
     // exchange: thread cl holds positions e*16+cl, wants cl*16+e
     unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + rl * (kRowLen * 8);
     {
@@ -140,12 +164,41 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
             v[2 * c + 1] = t.y;
         }
     }
-    ct_phase<4, BIG>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m);
+    if constexpr (PROT) {
+        // the exchange line this thread just read is free: stream its 16 output weights into it
+        // (cp.async, same chunk swizzle) while the second register phase runs
+        __syncwarp();
+        const u32 a0 = cl * 128 + ((cl & 7) << 4);
+        const unsigned char* om = reinterpret_cast<const unsigned char*>(p.omega + (size_t)mi * p.N + x0 + cl * 16);
+#pragma unroll
+        for (int c = 0; c < 8; c++)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(xrow + (a0 ^ (c << 4)))), "l"(om + c * 16) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    if constexpr (INJ)
+        ct_phase<4, BIG>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m, Inject{p.inj, p.n_inj, p.limb0 + limb, x0 + cl * 16, 0u, lc + 4, m.q});
+    else
+        ct_phase<4, BIG>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m);
 #pragma unroll
     for (int e = 0; e < 16; e++) v[e] = BIG ? canon2(reduce_lazy<BIG>(v[e], m), m.q) : canon3(reduce_lazy<BIG>(v[e], m), m.q);
     ulonglong2* out = reinterpret_cast<ulonglong2*>(rowp + cl * 16);
 #pragma unroll
     for (int e = 0; e < 8; e++) out[e] = make_ulonglong2(v[2 * e], v[2 * e + 1]);
+    if constexpr (PROT) {
+        // output side of the checksum, on the values just stored
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        const u32 a0 = cl * 128 + ((cl & 7) << 4);
+        AbftOut acc;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const ulonglong2 o = *reinterpret_cast<const ulonglong2*>(xrow + (a0 ^ (c << 4)));
+            acc.add(o.x, v[2 * c]);
+            acc.add(o.y, v[2 * c + 1]);
+        }
+        u64 s0, s1;
+        acc.value(s0, s1);
+        abft_commit<7>(p.abft, p.limb0 + limb, 1, s0, s1);
+    }
 }
 
 template <bool BIG>
@@ -226,15 +279,22 @@ k_inv_col(PassArgs p) {
 // ---------------------------------------------------------------- small N (2 <= N <= 2^11)
 // One CTA per limb, whole limb in shared memory, radix-2 stages, fully reduced.
 // Serves the prototype-sized cases (N = 16 .. 2048) of the Python bindings.
-template <bool INVERSE>
+template <bool INVERSE, bool PROT>
 __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
     extern __shared__ u64 a[];
     const u32 limb = blockIdx.x, mi = p.start_mod + limb % p.L;
     const B200Mod m = p.mods[mi];
     const ulonglong2* tw = p.tw + (size_t)mi * p.N;
     u64* base = p.data + (size_t)limb * p.N;
-    const u32 N = p.N, q_unused = 0; (void)q_unused;
-    for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon3(reduce_lazy<false>(base[i], m), m.q);
+    const u32 N = p.N;
+    const u64 nq = 0 - m.q;
+    AbftIn ain;
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) {
+        const u64 x = base[i];
+        if (PROT) ain.add(abft_w(i, (logn + 1) / 2), x);
+        a[i] = canon3(reduce_lazy<false>(x, m), m.q);
+    }
+    if (PROT) { u64 s0, s1; ain.value(s0, s1); abft_commit<5>(p.abft, p.limb0 + limb, 0, s0, s1); }
     __syncthreads();
     if (!INVERSE) {
         for (int s = 0; s < logn; s++) {
@@ -242,7 +302,11 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
             for (u32 b = threadIdx.x; b < N / 2; b += blockDim.x) {
                 const u32 i = b / t, j = b % t, x = 2 * i * t + j;
                 const ulonglong2 W = tw[mm + i];
-                const u64 X = a[x], T = canon2(shoup_mul(a[x + t], W.x, W.y, 0 - m.q), m.q);
+                u64 T = canon2(shoup_mul(a[x + t], W.x, W.y, nq), m.q);
+                if (PROT)
+                    for (u32 k = 0; k < p.n_inj; k++)
+                        if (p.inj[k].limb == p.limb0 + limb && p.inj[k].stage == (u32)s && p.inj[k].xa == x) T = inj_corrupt(T, p.inj[k], m.q);
+                const u64 X = a[x];
                 a[x] = canon2(X + T, m.q);
                 a[x + t] = canon2(X + m.q - T, m.q);
             }
@@ -256,27 +320,51 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
                 const ulonglong2 W = tw[mm + i];
                 const u64 U = a[x], V = a[x + t];
                 a[x] = canon2(U + V, m.q);
-                a[x + t] = canon2(shoup_mul(U + m.q - V, W.x, W.y, 0 - m.q), m.q);
+                a[x + t] = canon2(shoup_mul(U + m.q - V, W.x, W.y, nq), m.q);
             }
             __syncthreads();
         }
-        for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon2(shoup_mul(a[i], m.ninv, m.ninv_s, 0 - m.q), m.q);
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x) a[i] = canon2(shoup_mul(a[i], m.ninv, m.ninv_s, nq), m.q);
         __syncthreads();
     }
-    for (u32 i = threadIdx.x; i < N; i += blockDim.x) base[i] = a[i];
+    AbftOut aout;
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) {
+        base[i] = a[i];
+        if (PROT) aout.add(p.omega[(size_t)mi * N + i], a[i]);
+    }
+    if (PROT) { u64 s0, s1; aout.value(s0, s1); abft_commit<7>(p.abft, p.limb0 + limb, 1, s0, s1); }
+}
+
+// one thread per limb: compare the two checksums, publish verdict and sums, clear the counters
+__global__ void k_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_limbs) return;
+    const u64 q = mods[start_mod + i % L].q;
+    u64 val[2];
+    for (int side = 0; side < 2; side++) {
+        u64* c = counters + ((size_t)i * 2 + side) * kAbftStride;
+        u64 r = 0;                                   // Horner over the 20-bit digit sums, top digit first
+        for (int d = kAbftStride - 1; d >= 0; d--) {
+            r = (u64)((((unsigned __int128)r << 20) + c[d]) % q);
+            c[d] = 0;
+        }
+        val[side] = r;
+    }
+    if (verdict) verdict[i] = val[0] != val[1];
+    if (sums) { sums[2 * i] = val[0]; sums[2 * i + 1] = val[1]; }
 }
 
 // ---------------------------------------------------------------- dispatch
-template <int LC, int LA, bool BIG>
+template <int LC, int LA, bool BIG, bool PROT = false, bool INJ = false>
 static void launch_fwd2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
     dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kRowsPerCta, n_limbs);
     constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (mask & 1) k_fwd_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (mask & 1) k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
     if (mask & 2) {
-        cudaFuncSetAttribute(k_fwd_row<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
-        k_fwd_row<BIG><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
+        cudaFuncSetAttribute(k_fwd_row<BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
+        k_fwd_row<BIG, PROT, INJ><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
     }
 }
 template <int LC, int LA, bool BIG>
@@ -317,8 +405,8 @@ int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs,
     if (n_limbs == 0) return 0;
     if (logn >= 1 && logn <= 11) {
         size_t smem = sizeof(u64) << logn;
-        if (inverse) k_small<true><<<n_limbs, 256, smem, s>>>(a, logn);
-        else k_small<false><<<n_limbs, 256, smem, s>>>(a, logn);
+        if (inverse) k_small<true, false><<<n_limbs, 256, smem, s>>>(a, logn);
+        else k_small<false, false><<<n_limbs, 256, smem, s>>>(a, logn);
         return 0;
     }
     // grid.y limit is 65535 limbs per launch: split long batches
@@ -333,6 +421,34 @@ int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs,
         if (rc) return rc;
     }
     return 0;
+}
+
+template <bool BIG, bool INJ>
+static int launch_prot_t(const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+    switch (logn) {
+        case 12: launch_fwd2<4, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 13: launch_fwd2<5, 3, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 14: launch_fwd2<6, 3, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 15: launch_fwd2<7, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 16: launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 17: launch_fwd2<9, 5, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+    }
+    return -1;
+}
+
+int launch_ntt_protected(bool big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+    if (n_limbs == 0) return 0;
+    if (n_limbs > 32768) return -2;
+    if (logn >= 1 && logn <= 11) {
+        k_small<false, true><<<n_limbs, 256, sizeof(u64) << logn, s>>>(a, logn);
+        return 0;
+    }
+    if (a.n_inj) return big ? launch_prot_t<true, true>(a, logn, n_limbs, s) : launch_prot_t<false, true>(a, logn, n_limbs, s);
+    return big ? launch_prot_t<true, false>(a, logn, n_limbs, s) : launch_prot_t<false, false>(a, logn, n_limbs, s);
+}
+
+void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s) {
+    if (n_limbs) k_abft_finalize<<<(n_limbs + 127) / 128, 128, 0, s>>>(counters, mods, L, start_mod, n_limbs, verdict, sums);
 }
 
 }  // namespace b200

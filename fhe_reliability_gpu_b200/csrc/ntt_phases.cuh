@@ -30,10 +30,42 @@ struct TwList {
     __device__ __forceinline__ ulonglong2 get(int t, int g) const { return base[((1 << t) - 1 + g) * STRIDE]; }
 };
 
+// ---- fault-injection hook (protected path only) ---------------------------------------------
+// Mirrors the per-operation injection of rfhe_framewk/src/ntt_test/relia_ntt_sim.cpp:169-206:
+// the fault hits v = w * A[k + half] (the butterfly's product) of one chosen operation.  An
+// entry names the global stage and the coefficient index of the butterfly's upper ("a") input.
+struct InjEntry {
+    u32 limb;      // limb index inside the call (poly * L + l)
+    u32 stage;     // 0 .. log_n - 1, SEAL stage order (m = 2^stage groups)
+    u32 xa;        // coefficient index of the a-input: 2*i*gap + j for group i, offset j
+    u32 kind;      // 1: v = (v ^ payload) mod q (SBF/DBF, :118-127)   2: v = payload mod q (MLF, :128-130)
+    u64 payload;
+};
+struct NoInject {
+    static constexpr bool on = false;
+    __device__ __forceinline__ u64 apply(int, int, u64 T) const { return T; }
+};
+__device__ __forceinline__ u64 inj_corrupt(u64 T, const InjEntry& e, u64 q) {
+    u64 v = T % q;
+    return e.kind == 1 ? (v ^ e.payload) % q : e.payload % q;
+}
+// element e of the phase sits at coefficient index base + (e << shift); phase sub-stage t is global stage stage0 + t
+struct Inject {
+    static constexpr bool on = true;
+    const InjEntry* e;
+    u32 n, limb, base, shift, stage0;
+    u64 q;
+    __device__ __forceinline__ u64 apply(int t, int a, u64 T) const {
+        for (u32 i = 0; i < n; i++)
+            if (e[i].limb == limb && e[i].stage == stage0 + (u32)t && e[i].xa == base + ((u32)a << shift)) T = inj_corrupt(T, e[i], q);
+        return T;
+    }
+};
+
 // Forward Cooley-Tukey phase.  In: any 64-bit words (congruent to the wanted
 // residues).  Out: values < (B0 + 2*LR) q, B0 = reduce_lazy's bound.
-template <int LR, bool BIG, class TW>
-__device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m) {
+template <int LR, bool BIG, class TW, class INJ = NoInject>
+__device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m, const INJ& inj = INJ()) {
     constexpr int R = 1 << LR;
     const u64 q = m.q, two_q = q << 1, nq = 0 - q;
 #pragma unroll
@@ -47,7 +79,8 @@ __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const 
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int a = g * 2 * half + i, b = a + half;
-                const u64 T = shoup_mul(v[b], W.x, W.y, nq);
+                u64 T = shoup_mul(v[b], W.x, W.y, nq);
+                if (INJ::on) T = inj.apply(t, a, T);
                 const u64 X = v[a];
                 v[a] = X + T;
                 v[b] = X - T + two_q;

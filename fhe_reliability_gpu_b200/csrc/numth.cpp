@@ -99,5 +99,30 @@ void tables(int log_n, uint64_t q, uint64_t psi, uint64_t* rp, uint64_t* rps, ui
     }
 }
 
+void forward_ntt_host(uint64_t* a, int log_n, uint64_t q, const uint64_t* rp) {
+    const uint64_t N = (uint64_t)1 << log_n;
+    uint64_t t = N >> 1;
+    for (uint64_t m = 1; m < N; m <<= 1, t >>= 1)
+        for (uint64_t i = 0; i < m; i++) {
+            const uint64_t w = rp[m + i];
+            uint64_t* x = a + 2 * i * t;
+            for (uint64_t j = 0; j < t; j++) {
+                const uint64_t u = x[j], v = mulmod(x[j + t], w, q);
+                x[j] = u + v >= q ? u + v - q : u + v;
+                x[j + t] = u >= v ? u - v : u + q - v;
+            }
+        }
+}
+
+void abft_output_weights(int log_n, uint64_t q, uint64_t psi, uint64_t* omega) {
+    const uint64_t N = (uint64_t)1 << log_n;
+    std::vector<uint64_t> irp(N);
+    tables(log_n, q, psi, nullptr, nullptr, irp.data(), nullptr);
+    for (uint64_t i = 0; i < N; i++) omega[i] = abft_input_weight(i, log_n) % q;
+    forward_ntt_host(omega, log_n, q, irp.data());
+    const uint64_t ninv = invmod(N % q, q);
+    for (uint64_t i = 0; i < N; i++) omega[i] = mulmod(omega[i], ninv, q);
+}
+
 }  // namespace nt
 }  // namespace b200

@@ -45,5 +45,21 @@ void const_ratio(uint64_t q, uint64_t ratio[2]);
 // rp/rps/irp/irps may be null
 void tables(int log_n, uint64_t q, uint64_t psi, uint64_t* rp, uint64_t* rps, uint64_t* irp, uint64_t* irps);
 
+// SEAL-order forward negacyclic NTT on the host (table construction only, O(N log N) 128-bit mulmods)
+void forward_ntt_host(uint64_t* a, int log_n, uint64_t q, const uint64_t* rp);
+
+// ABFT weighted checksum (rfhe_framewk/src/negaclic_ntt.py:130-149 ecc_check): input weights are
+// generate_weights(N) (:8-13): w_i = (i mod p) + 1 + (i div p) + 1 with period p = sqrt(N)
+// (p = 2^ceil(log_n/2) when N is not a perfect square).  Small (< 2^10), so the device
+// accumulates sum w_i x_i with two carry-free IMAD.WIDE per coefficient.
+inline int abft_period_log(int log_n) { return (log_n + 1) / 2; }
+inline uint64_t abft_input_weight(uint64_t i, int log_n) {
+    const int pl = abft_period_log(log_n);
+    return (i & (((uint64_t)1 << pl) - 1)) + (i >> pl) + 2;
+}
+// omega with  sum_k omega_k NTT(x)_k == sum_i w_i x_i (mod q) for every x, NTT in SEAL (bit-reversed)
+// output order:  omega = N^-1 * NTT_{psi^-1}(w)  (the prototype's w_hat = INTT(D^-1 w), :137-140)
+void abft_output_weights(int log_n, uint64_t q, uint64_t psi, uint64_t* omega);
+
 }  // namespace nt
 }  // namespace b200

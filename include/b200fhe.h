@@ -105,6 +105,45 @@ int b200fhe_nwt_backward_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly
 int b200fhe_host_alloc(void** p, size_t bytes);
 int b200fhe_host_free(void* p);
 
+/* ---- protected forward NTT with fused ABFT checksum (config C4) ------------- */
+
+/* One injected fault, in the operation numbering of
+ * rfhe_framewk/src/ntt_test/relia_ntt_sim.cpp:169-206 (the product v = w * A[k+half]
+ * of one butterfly is corrupted before it is used): `stage` in [0, log_n) is the
+ * SEAL stage (m = 2^stage groups), `butterfly` in [0, N/2) counts butterflies of
+ * that stage in loop order (group-major).  kind 1: v = (v XOR payload) mod q (SBF /
+ * DBF, :118-127); kind 2: v = payload mod q (MLF, :128-130). */
+typedef struct b200fhe_inject {
+    uint32_t limb;       /* poly * L + l inside the call */
+    uint32_t stage;
+    uint64_t butterfly;
+    uint32_t kind;
+    uint32_t reserved;
+    uint64_t payload;
+} b200fhe_inject;
+#define B200FHE_MAX_INJECT 16
+
+/* Forward transform as b200fhe_nwt_forward, plus the weighted checksum of
+ * rfhe_framewk/src/negaclic_ntt.py:130-149 (sum_i w_i a_i == sum_k w^_k a^_k, weights
+ * generate_weights(N) :8-13) accumulated inside the first load and the last store
+ * of the transform -- the GPU form of the protected four-step NTT prototyped in
+ * reliability_test/four_step_ntt_prot.py:185-252 and evaluated in relia_ntt_sim.cpp.
+ * d_verdict[n_poly*L] receives 0 (checksums agree) or 1 (fault detected); d_sums
+ * (optional, [n_poly*L][2]) receives the input- and output-side checksum.  h_plan /
+ * n_plan (optional, host memory, <= B200FHE_MAX_INJECT) inject faults.  One
+ * protected call may be in flight per context. */
+int b200fhe_nwt_forward_protected(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_poly, size_t L, size_t start_mod,
+                                  uint32_t* d_verdict, uint64_t* d_sums, const b200fhe_inject* h_plan, size_t n_plan,
+                                  void* stream);
+
+/* Host-buffer form: h_verdict [n_poly*L], h_sums optional [n_poly*L][2]. */
+int b200fhe_nwt_forward_protected_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly, size_t L, size_t start_mod,
+                                       uint32_t* h_verdict, uint64_t* h_sums, const b200fhe_inject* h_plan, size_t n_plan);
+
+/* The ABFT weights of modulus idx: w[N] (input side) and w_hat[N] (output side, SEAL
+ * output order); either pointer may be NULL. */
+int b200fhe_abft_weights(b200fhe_ctx* ctx, int idx, uint64_t* w, uint64_t* w_hat);
+
 /* ---- ct x pt multiply-accumulate (config C3) ------------------------------- */
 
 /* out[p][l][i] = sum_{k<n_terms} ct_k[p][l][i] * pt_k[l][i] mod q_{start_mod+l}, NTT domain.

@@ -50,6 +50,9 @@ def lib():
             ("orc_ntt_inverse_harvey", None, [U64P, i32, u64, U64P, U64P]),
             ("orc_ntt_forward_batch", None, [U64P, i32, i32, U64P, U64P, U64P]),
             ("orc_ntt_inverse_batch", None, [U64P, i32, i32, U64P, U64P, U64P]),
+            ("orc_abft_weights", None, [i32, U64P]),
+            ("orc_abft_output_weights", None, [i32, u64, U64P, U64P, U64P]),
+            ("orc_ntt_forward_protected", i32, [U64P, i32, u64, U64P, U64P, U64P, C.c_void_p, i32, U64P, U64P]),
             ("orc_negacyclic_mul_naive", None, [U64P, U64P, U64P, u64, u64]),
             ("orc_pmult_accum", None, [U64P, U64P, U64P, i32, i32, i32, u64, U64P]),
             ("orc_bconv_hps", None, [U64P, U64P, i32, i32, u64, U64P, U64P]),
@@ -142,6 +145,32 @@ def ntt_inverse_batch(a, tabs, inplace=False):
     irp = np.stack([t.irp for t in tabs]); irps = np.stack([t.irps for t in tabs])
     lib().orc_ntt_inverse_batch(_p(a), tabs[0].logn, L, _p(q), _p(irp), _p(irps))
     return a
+
+
+class OrcInject(C.Structure):
+    _fields_ = [("stage", C.c_uint32), ("kind", C.c_uint32), ("butterfly", C.c_uint64), ("payload", C.c_uint64)]
+
+
+def abft_weights(tab):
+    """(w, omega) for one modulus: generate_weights(N) and its transformed weights (SEAL output order)."""
+    w = np.zeros(tab.N, dtype=np.uint64); om = np.zeros(tab.N, dtype=np.uint64)
+    lib().orc_abft_weights(tab.logn, _p(w))
+    lib().orc_abft_output_weights(tab.logn, tab.q, _p(tab.irp), _p(w), _p(om))
+    return w, om
+
+
+def ntt_forward_protected(a, tab, plan=(), weights=None):
+    """plan: iterable of (stage, butterfly, kind, payload).  Returns (out, detected, lhs, rhs)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64).copy()
+    w, om = weights if weights is not None else abft_weights(tab)
+    plan = list(plan)
+    arr = (OrcInject * max(len(plan), 1))()
+    for i, (stage, bf, kind, payload) in enumerate(plan):
+        arr[i] = OrcInject(stage, kind, bf, payload)
+    lhs, rhs = C.c_uint64(), C.c_uint64()
+    det = lib().orc_ntt_forward_protected(_p(a), tab.logn, tab.q, _p(tab.rp), _p(w), _p(om), C.cast(arr, C.c_void_p), len(plan),
+                                          C.byref(lhs), C.byref(rhs))
+    return a, bool(det), int(lhs.value), int(rhs.value)
 
 
 def pmult_accum(ct, pt, q):
