@@ -39,6 +39,12 @@ SIGNATURES = {
     "b200fhe_abft_weights": (i32, [vp, i32, U64P, U64P]),
     "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
+    "b200fhe_bconv_create": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, C.POINTER(vp)]),
+    "b200fhe_bconv_destroy": (i32, [vp]),
+    "b200fhe_bconv_scale": (i32, [vp, vp, vp, sz, sz, vp]),
+    "b200fhe_bconv_contract": (i32, [vp, vp, vp, sz, sz, vp]),
+    "b200fhe_bconv_modup": (i32, [vp, vp, vp, vp]),
+    "b200fhe_bconv_modup_host": (i32, [vp, U64P, U64P]),
     "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
     "b200fhe_host_alloc": (i32, [C.POINTER(vp), sz]),
     "b200fhe_host_free": (i32, [vp]),
@@ -199,6 +205,41 @@ Context.nwt_forward_protected_host = _nwt_forward_protected_host
 Context.abft_weights = _abft_weights
 Context.pmult_accum_host = _pmult_accum_host
 Context.pmult_accum = _pmult_accum
+
+
+class BaseConv:
+    """ModUp plan (b200fhe_bconv): source base = context moduli src_idx, targets = context moduli dst_idx."""
+
+    def __init__(self, ctx, src_idx, dst_idx):
+        self.ctx, self.src, self.dst = ctx, list(src_idx), list(dst_idx)
+        self.m, self.K, self.N = len(self.src), len(self.dst), ctx.N
+        h = vp()
+        check(lib().b200fhe_bconv_create(ctx._h, (i32 * self.m)(*self.src), self.m, (i32 * self.K)(*self.dst), self.K, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200fhe_bconv_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def scale(self, x_ptr, y_ptr, j0, count, stream=0):
+        check(lib().b200fhe_bconv_scale(self._h, x_ptr, y_ptr, j0, count, stream))
+
+    def contract(self, y_ptr, out_ptr, k0, kcount, stream=0):
+        check(lib().b200fhe_bconv_contract(self._h, y_ptr, out_ptr, k0, kcount, stream))
+
+    def modup(self, in_ptr, out_ptr, stream=0):
+        check(lib().b200fhe_bconv_modup(self._h, in_ptr, out_ptr, stream))
+
+    def modup_host(self, x):
+        """x [m][N] uint64 residues mod the source moduli -> [K][N] residues mod the targets."""
+        x = np.ascontiguousarray(x, dtype=np.uint64)
+        assert x.shape == (self.m, self.N)
+        out = np.zeros((self.K, self.N), dtype=np.uint64)
+        check(lib().b200fhe_bconv_modup_host(self._h, _p(x), _p(out)))
+        return out
 
 
 def flip_bit(ptr, idx, bit, stream=0):

@@ -558,6 +558,117 @@ extern "C" int b200fhe_pmult_accum_host(b200fhe_ctx* c, const uint64_t* h_ct, co
     return 0;
 }
 
+// ---------------------------------------------------------------- base conversion
+extern "C" int b200fhe_bconv_destroy(b200fhe_bconv* p) {
+    if (!p) return 0;
+    if (p->ctx) cudaSetDevice(p->ctx->device);
+    if (p->d_src) cudaFree(p->d_src);
+    if (p->d_dst) cudaFree(p->d_dst);
+    if (p->d_inv) cudaFree(p->d_inv);
+    if (p->d_hat) cudaFree(p->d_hat);
+    if (p->d_y) cudaFree(p->d_y);
+    if (p->d_io) cudaFree(p->d_io);
+    delete p;
+    return 0;
+}
+
+extern "C" int b200fhe_bconv_create(b200fhe_ctx* c, const int* src_idx, int m, const int* dst_idx, int K, b200fhe_bconv** out) {
+    if (!c || !src_idx || !dst_idx || !out || m < 1 || K < 1 || m > 64) return b200_set_err(B200FHE_EINVAL, "bconv_create: bad arguments");
+    std::vector<u32> src(m), dst(K);
+    for (int j = 0; j < m; j++) {
+        if (src_idx[j] < 0 || src_idx[j] >= c->L || !c->moduli[src_idx[j]]) return b200_set_err(B200FHE_EINVAL, "bconv_create: bad source index %d", src_idx[j]);
+        for (int i = 0; i < j; i++)
+            if (src_idx[i] == src_idx[j]) return b200_set_err(B200FHE_EINVAL, "bconv_create: repeated source modulus");
+        src[j] = (u32)src_idx[j];
+    }
+    for (int k = 0; k < K; k++) {
+        if (dst_idx[k] < 0 || dst_idx[k] >= c->L || !c->moduli[dst_idx[k]]) return b200_set_err(B200FHE_EINVAL, "bconv_create: bad target index %d", dst_idx[k]);
+        dst[k] = (u32)dst_idx[k];
+    }
+    std::vector<ulonglong2> inv(m);
+    std::vector<uint64_t> hat((size_t)K * m);
+    for (int j = 0; j < m; j++) {
+        const uint64_t pj = c->moduli[src[j]];
+        uint64_t h = 1;
+        for (int i = 0; i < m; i++)
+            if (i != j) h = nt::mulmod(h, c->moduli[src[i]] % pj, pj);
+        const uint64_t iv = nt::invmod(h, pj);
+        inv[j] = make_ulonglong2(iv, nt::shoup(iv, pj));
+        for (int k = 0; k < K; k++) {
+            const uint64_t qk = c->moduli[dst[k]];
+            uint64_t g = 1;
+            for (int i = 0; i < m; i++)
+                if (i != j) g = nt::mulmod(g, c->moduli[src[i]] % qk, qk);
+            hat[(size_t)k * m + j] = (g & 0x3fffffffull) | ((g >> 30) << 32);
+        }
+    }
+    CK(cudaSetDevice(c->device));
+    b200fhe_bconv* p = new b200fhe_bconv();
+    p->ctx = c; p->m = m; p->K = K;
+    cudaError_t e = cudaMalloc(&p->d_src, sizeof(u32) * m);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_dst, sizeof(u32) * K);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_inv, sizeof(ulonglong2) * m);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_hat, sizeof(uint64_t) * K * m);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_y, sizeof(uint64_t) * m * c->N);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_src, src.data(), sizeof(u32) * m, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_dst, dst.data(), sizeof(u32) * K, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_inv, inv.data(), sizeof(ulonglong2) * m, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_hat, hat.data(), sizeof(uint64_t) * K * m, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        b200fhe_bconv_destroy(p);
+        return b200_set_err(B200FHE_ECUDA, "bconv_create: %s", cudaGetErrorString(e));
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" int b200fhe_bconv_scale(b200fhe_bconv* p, const uint64_t* d_x, uint64_t* d_y, size_t j0, size_t count, void* stream) {
+    if (!p || (count && (!d_x || !d_y)) || j0 + count > (size_t)p->m) return b200_set_err(B200FHE_EINVAL, "bconv_scale: bad arguments");
+    CK(cudaSetDevice(p->ctx->device));
+    launch_bconv_scale((const u64*)d_x, (u64*)d_y, p->ctx->d_mods, p->d_src, p->d_inv, (u32)p->ctx->N, (u32)j0, (u32)count, (cudaStream_t)stream);
+    if (count) g_launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200fhe_bconv_contract(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t k0, size_t kcount, void* stream) {
+    if (!p || (kcount && (!d_y || !d_out)) || k0 + kcount > (size_t)p->K) return b200_set_err(B200FHE_EINVAL, "bconv_contract: bad arguments");
+    CK(cudaSetDevice(p->ctx->device));
+    int rc = launch_bconv_contract((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, (const u64*)p->d_hat, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
+                                   (u32)k0, (u32)kcount, (cudaStream_t)stream);
+    if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_contract: source base too large for shared memory (m=%d)", p->m);
+    if (kcount) g_launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200fhe_bconv_modup(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_out, void* stream) {
+    if (!p) return b200_set_err(B200FHE_EINVAL, "bconv_modup: null plan");
+    int rc = b200fhe_bconv_scale(p, d_in, (uint64_t*)p->d_y, 0, p->m, stream);
+    if (rc) return rc;
+    return b200fhe_bconv_contract(p, (const uint64_t*)p->d_y, d_out, 0, p->K, stream);
+}
+
+extern "C" int b200fhe_bconv_modup_host(b200fhe_bconv* p, const uint64_t* h_in, uint64_t* h_out) {
+    if (!p || !h_in || !h_out) return b200_set_err(B200FHE_EINVAL, "bconv_modup_host: null argument");
+    b200fhe_ctx* c = p->ctx;
+    CK(cudaSetDevice(c->device));
+    const size_t wi = (size_t)p->m * c->N, wo = (size_t)p->K * c->N;
+    if (p->io_words < wi + wo) {
+        if (p->d_io) cudaFree(p->d_io);
+        p->d_io = nullptr; p->io_words = 0;
+        CK(cudaMalloc(&p->d_io, sizeof(uint64_t) * (wi + wo)));
+        p->io_words = wi + wo;
+    }
+    cudaStream_t s = c->own_stream;
+    CK(cudaMemcpyAsync(p->d_io, h_in, sizeof(uint64_t) * wi, cudaMemcpyHostToDevice, s));
+    int rc = b200fhe_bconv_modup(p, (const uint64_t*)p->d_io, (uint64_t*)(p->d_io + wi), s);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_out, p->d_io + wi, sizeof(uint64_t) * wo, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+
 // ---------------------------------------------------------------- fault injection
 __global__ void k_flip_bit(u64* data, size_t idx, unsigned bit) { data[idx] ^= (1ull << bit); }
 

@@ -48,6 +48,11 @@ void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_m
 int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
                  u32 start_mod, int accumulate, cudaStream_t s, unsigned long long* launches);
 
+int launch_bconv_scale(const u64* x, u64* y, const B200Mod* mods, const u32* src_idx, const ulonglong2* inv, u32 N, u32 j0, u32 count,
+                       cudaStream_t s);
+int launch_bconv_contract(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const u64* hat, u32 N, u32 m, u32 K, u32 k0,
+                          u32 kcount, cudaStream_t s);
+
 }  // namespace b200
 
 struct b200fhe_ctx {
@@ -77,4 +82,17 @@ struct b200fhe_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
     std::vector<cudaEvent_t> ev;
+};
+
+// Base-conversion plan: constants of one (source base -> target moduli) pair, resident on the context's device.
+struct b200fhe_bconv {
+    b200fhe_ctx* ctx = nullptr;
+    int m = 0, K = 0;
+    u32* d_src = nullptr;            // [m] modulus indices
+    u32* d_dst = nullptr;            // [K]
+    ulonglong2* d_inv = nullptr;     // [m] (P/p_j)^-1 mod p_j with Shoup quotient
+    u64* d_hat = nullptr;            // [K][m] (P/p_j) mod q_k, 30-bit halves packed
+    u64* d_y = nullptr;              // [m][N] scratch for the single-GPU path
+    u64* d_io = nullptr;             // host-buffer path staging, grown on demand
+    size_t io_words = 0;
 };

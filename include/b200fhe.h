@@ -162,6 +162,30 @@ int b200fhe_pmult_accum(b200fhe_ctx* ctx, const uint64_t* const* ct, const uint6
 int b200fhe_pmult_accum_host(b200fhe_ctx* ctx, const uint64_t* h_ct, const uint64_t* h_pt, size_t n_terms, uint64_t* h_out,
                              size_t n_poly, size_t L, size_t start_mod);
 
+/* ---- RNS base conversion / ModUp (config C5) --------------------------------- */
+
+typedef struct b200fhe_bconv b200fhe_bconv;
+
+/* Conversion plan from the source base {p_j = modulus src_idx[j]} (one key-switch digit) to the target
+ * moduli {q_k = modulus dst_idx[k]} of the same context.  Fast (HPS) conversion, the algorithm of SEAL
+ * BaseConverter::fast_convert_array / Phantom DRNSTool ModUp that relinearize_inplace and rotate_inplace
+ * run (reliability_test/dotprod_test.cu:114,146); in-tree spec rfhe_framewk/src/baseConv.py:10-40:
+ *   y_j = x_j (P/p_j)^-1 mod p_j ;  out_k = sum_j y_j ((P/p_j) mod q_k) mod q_k      (= x + e P, 0 <= e < m). */
+int b200fhe_bconv_create(b200fhe_ctx* ctx, const int* src_idx, int m, const int* dst_idx, int K, b200fhe_bconv** out);
+int b200fhe_bconv_destroy(b200fhe_bconv* plan);
+
+/* Step 1 on `count` source limbs starting at source position j0: d_y[c][i] = d_x[c][i] (P/p_j)^-1 mod p_j,
+ * j = j0 + c.  Coefficient domain in, coefficient domain out; buffers are [count][N]. */
+int b200fhe_bconv_scale(b200fhe_bconv* plan, const uint64_t* d_x, uint64_t* d_y, size_t j0, size_t count, void* stream);
+
+/* Step 2 for target positions [k0, k0 + kcount): d_out[c][i] = sum_j d_y[j][i] ((P/p_j) mod q_k) mod q_k,
+ * k = k0 + c.  d_y is the full [m][N] scaled digit (after the limb all-gather when sharded). */
+int b200fhe_bconv_contract(b200fhe_bconv* plan, const uint64_t* d_y, uint64_t* d_out, size_t k0, size_t kcount, void* stream);
+
+/* Both steps on one GPU: d_in [m][N] -> d_out [K][N]. */
+int b200fhe_bconv_modup(b200fhe_bconv* plan, const uint64_t* d_in, uint64_t* d_out, void* stream);
+int b200fhe_bconv_modup_host(b200fhe_bconv* plan, const uint64_t* h_in, uint64_t* h_out);
+
 /* Measurement hooks (bench.py): one pass of the two-kernel transform
  * (pass 1 = first kernel, 2 = second), and the number of kernels this library
  * has launched in this process. */
