@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 using namespace b200;
 
@@ -75,6 +76,7 @@ static B200Mod make_mod(uint64_t q, int log_n, uint64_t itw1, uint64_t n_inv) {
     m.big = m.bits > 36;
     m.mprec = m.big ? (uint32_t)((((nt::u128)1) << (m.bits + 31)) / q) : 0;
     m.pshift = m.big ? m.bits - 33 : 0;
+    m.q3 = 3 * q;
     (void)log_n;
     return m;
 }
@@ -238,13 +240,26 @@ extern "C" int b200fhe_ctx_moduli(const b200fhe_ctx* c, uint64_t* out) {
 static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py's gpu_launches)
 extern "C" unsigned long long b200fhe_launch_count(void) { return g_launches; }
 
-// Polynomials per launch pair: the column and row passes of one chunk run
-// back to back so the lazily-reduced intermediate stays in the 126 MB L2
-// instead of making a second HBM round trip.
+// Polynomials per launch on the device-resident path.  The transform is bound by the integer
+// multiplier pipe, not by HBM (profiles/r1e_*), so keeping the lazily-reduced intermediate inside
+// the 126 MB L2 buys nothing while short launches lose 13 % to wave tails (chunk sweep in
+// profiles/r1e_chunk_sweep.md): the whole batch goes out as one launch pair per 32768 limbs.
 static size_t chunk_polys(const b200fhe_ctx* c, size_t L) {
+    static const size_t budget = [] {
+        const char* e = getenv("B200FHE_CHUNK_MB");
+        return (size_t)(e && atoi(e) > 0 ? atoi(e) : 1 << 20) << 20;
+    }();
     const size_t bytes_per_poly = L * c->N * sizeof(uint64_t);
-    const size_t budget = (size_t)40 << 20;
     size_t n = budget / (bytes_per_poly ? bytes_per_poly : 1);
+    const size_t cap = 32768 / (L ? L : 1);          // grid.y limit of one launch
+    if (n > cap) n = cap;
+    return n ? n : 1;
+}
+// Polynomials per pipeline stage of the host-buffer path: 40 MiB pieces keep H2D, kernels and D2H
+// of neighbouring pieces overlapped on the three streams.
+static size_t host_chunk_polys(const b200fhe_ctx* c, size_t L) {
+    const size_t bytes_per_poly = L * c->N * sizeof(uint64_t);
+    size_t n = ((size_t)40 << 20) / (bytes_per_poly ? bytes_per_poly : 1);
     return n ? n : 1;
 }
 
@@ -267,7 +282,7 @@ static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, siz
     a.N = (u32)c->N;
     a.L = (u32)L;
     a.start_mod = (u32)start;
-    const size_t step = (mask == 3) ? chunk_polys(c, L) : n_poly;
+    const size_t step = chunk_polys(c, L);
     for (size_t p0 = 0; p0 < n_poly; p0 += step) {
         const size_t np = n_poly - p0 < step ? n_poly - p0 : step;
         a.data = (u64*)d + p0 * L * c->N;
@@ -342,7 +357,7 @@ static int run_ntt_host(b200fhe_ctx* c, bool inverse, uint64_t* h, size_t n_poly
         CK(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
     }
-    const size_t step = chunk_polys(c, L);
+    const size_t step = host_chunk_polys(c, L);
     const size_t n_chunks = (n_poly + step - 1) / step;
     if (c->ev.size() < 2 * n_chunks) {
         size_t old = c->ev.size();

@@ -31,6 +31,8 @@ struct __align__(16) B200Mod {
     u32 big;      // 1 if q >= 2^36 (32-bit quotient estimate valid for all 64-bit v)
     u32 bits;     // bit length of q
     u32 pshift;   // bits - 33: floor(v/q) ~ umulhi(v >> 32, mprec) >> pshift
+    u64 q3;       // 3q, kept in memory so ptxas cannot rematerialise it as an IMAD.WIDE (multiplier pipe)
+    u64 pad_;
 };
 
 __device__ __forceinline__ u64 pack64(u32 lo, u32 hi) {
@@ -56,6 +58,36 @@ __device__ __forceinline__ u64 shoup_mul(u64 y, u64 w, u64 ws, u64 nq) {
     unpack64(k, kl, kh);
     unpack64(nq, nl, nh);
     u64 r;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(r) : "r"(yl), "r"(wl));
+    asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(r) : "r"(kl), "r"(nl));
+    unpack64(r, rl, rh);
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(yl), "r"(wh));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(yh), "r"(wl));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kl), "r"(nh));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kh), "r"(nl));
+    return pack64(rl, rh);
+}
+
+// Lazy Shoup product: y arbitrary 64-bit, w < q  ->  y*w mod q + {0,q,2q}  (< 3q).
+// The quotient estimate drops the yl*sl partial product (error <= 1), so the whole
+// multiply is 5 IMAD.WIDE + 4 IMAD -- 28 issue cycles of the 16-lane integer-multiply
+// pipe, which is the binding unit of the NTT on sm_100a (IMAD.WIDE occupies it for 4
+// cycles per warp, IMAD for 2: profiles/r1d_pipe_calibration.md).  Both cross terms use
+// mad.wide with a zero-extended 32-bit addend, which cannot overflow 64 bits, so no carry
+// chain is needed: s2 = yh*sl + lo32(yl*sh), k = yh*sh + hi32(yl*sh) + hi32(s2).
+__device__ __forceinline__ u64 shoup_mul_lazy(u64 y, u64 w, u64 ws, u64 nq) {
+    u32 yl, yh, wl, wh, sl, sh, nl, nh, c1l, c1h, kl, kh, rl, rh;
+    unpack64(y, yl, yh);
+    unpack64(w, wl, wh);
+    unpack64(ws, sl, sh);
+    unpack64(nq, nl, nh);
+    u64 c1, s2, k, r;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(c1) : "r"(yl), "r"(sh));
+    unpack64(c1, c1l, c1h);
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(s2) : "r"(yh), "r"(sl), "l"((u64)c1l));
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(k) : "r"(yh), "r"(sh), "l"((u64)c1h));
+    k += (s2 >> 32);
+    unpack64(k, kl, kh);
     asm("mul.wide.u32 %0, %1, %2;" : "=l"(r) : "r"(yl), "r"(wl));
     asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(r) : "r"(kl), "r"(nl));
     unpack64(r, rl, rh);

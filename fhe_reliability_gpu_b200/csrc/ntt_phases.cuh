@@ -63,27 +63,34 @@ struct Inject {
 };
 
 // Forward Cooley-Tukey phase.  In: any 64-bit words (congruent to the wanted
-// residues).  Out: values < (B0 + 2*LR) q, B0 = reduce_lazy's bound.
+// residues).  Out: values < 16q.  Lazy products are < 3q, so the X path grows by 3q per
+// sub-stage from reduce_lazy's bound B0 <= 3: 15q after four sub-stages; a fifth
+// sub-stage (LR = 5, the N = 2^17 column pass) re-reduces its X inputs first.
 template <int LR, bool BIG, class TW, class INJ = NoInject>
 __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m, const INJ& inj = INJ()) {
     constexpr int R = 1 << LR;
-    const u64 q = m.q, two_q = q << 1, nq = 0 - q;
+    const u64 q = m.q, q3 = m.q3, nq = 0 - q;
 #pragma unroll
     for (int e = 0; e < R / 2; e++) v[e] = reduce_lazy<BIG>(v[e], m);   // X half of sub-stage 0
 #pragma unroll
     for (int t = 0; t < LR; t++) {
         const int half = R >> (t + 1);
+        if (t == 4) {                          // X inputs would pass 16q - 3q: bring them back below 3q
+#pragma unroll
+            for (int e = 0; e < R; e++)
+                if ((e & half) == 0) v[e] = reduce_lazy<BIG>(v[e], m);
+        }
 #pragma unroll
         for (int g = 0; g < (1 << t); g++) {
             const ulonglong2 W = tw.get(t, g);
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int a = g * 2 * half + i, b = a + half;
-                u64 T = shoup_mul(v[b], W.x, W.y, nq);
+                u64 T = shoup_mul_lazy(v[b], W.x, W.y, nq);
                 if (INJ::on) T = inj.apply(t, a, T);
                 const u64 X = v[a];
                 v[a] = X + T;
-                v[b] = X - T + two_q;
+                v[b] = X - T + q3;
             }
         }
     }
@@ -108,9 +115,10 @@ __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const 
 #pragma unroll
             for (int e = 0; e < R; e++)
                 if ((e & phalf) == 0) v[e] = reduce_lazy<BIG>(v[e], m);
-            bound = LazyBound<BIG>::value;
+            bound = 3;                         // the product elements stay below 3q
         }
-        const u64 bq = q * (u64)bound;
+        // bound is 2^k or 3*2^k: shifts of q or of the memory-resident 3q (no multiplier-pipe rematerialisation)
+        const u64 bq = (bound % 3 == 0) ? (m.q3 << (31 - __builtin_clz(bound / 3))) : (q << (31 - __builtin_clz(bound)));
         const bool fold = LAST && (t == 0);
 #pragma unroll
         for (int g = 0; g < (1 << t); g++) {
@@ -122,14 +130,14 @@ __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const 
                 const int a = g * 2 * half + i, b = a + half;
                 const u64 U = v[a], V = v[b];
                 const u64 S = U + V;
-                v[b] = shoup_mul(U - V + bq, W.x, W.y, nq);
-                v[a] = fold ? shoup_mul(S, m.ninv, m.ninv_s, nq) : S;
+                v[b] = shoup_mul_lazy(U - V + bq, W.x, W.y, nq);
+                v[a] = fold ? shoup_mul_lazy(S, m.ninv, m.ninv_s, nq) : S;
             }
         }
         bound *= 2;
     }
     if (LAST) {
 #pragma unroll
-        for (int e = 0; e < R; e++) v[e] = canon2(v[e], q);
+        for (int e = 0; e < R; e++) v[e] = canon3(v[e], q);
     }
 }
