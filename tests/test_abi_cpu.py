@@ -77,3 +77,30 @@ def test_no_cpu_fallback_without_a_device(pkg):
     with pytest.raises(pkg.B200FHEError) as e:
         pkg.Context(12, pkg.primes_create(4096, [60]))
     assert "no CUDA device" in str(e.value) or "CUDA" in str(e.value)
+
+
+def test_harness_cli_argument_errors_without_a_gpu():
+    """ntt_test / dotprod_test reject bad argv before touching CUDA (ntt_test.cu:29-38,202-216;
+    dotprod_test.cu:190-194): exit code 1 and the usage / error text, on any machine."""
+    import subprocess
+    exe = os.path.join(ROOT, "harness", "bin", "ntt_test")
+    dp = os.path.join(ROOT, "harness", "bin", "dotprod_test")
+    if not (os.path.exists(exe) and os.path.exists(dp)):
+        pytest.skip("harness not built (run __graft_entry__.build())")
+    p = subprocess.run([exe, "12", "1"], capture_output=True, text=True)
+    assert p.returncode == 1 and "Usage:" in p.stderr and "<log_dim> <batch_size> <num_flips> <num_target_symbols>" in p.stderr
+    p = subprocess.run([exe, "12", "1", "0", "1"], capture_output=True, text=True)
+    assert p.returncode == 1 and "must be >= 1" in p.stderr
+    p = subprocess.run([exe, "12", "1", "65", "1"], capture_output=True, text=True)
+    assert p.returncode == 1 and "exceeds bits per symbol (64)" in p.stderr
+    p = subprocess.run([dp], capture_output=True, text=True)
+    assert p.returncode == 1 and "<bits_per_symbol> <num_symbols>" in p.stderr
+
+
+def test_shim_header_exposes_the_phantom_names_the_harness_uses():
+    """shim/phantom.h must keep every name reliability_test/ntt_test.cu:40-68,88,95 spells."""
+    src = open(os.path.join(ROOT, "shim", "phantom.h")).read()
+    for name in ["cuda_stream_wrapper", "get_stream", "make_cuda_auto_ptr", "struct DModulus", "class DNTTTable",
+                 "void init(", "void set(", "CoeffModulus", "Create(", "class NTT", "get_from_root_powers()",
+                 "get_from_root_powers_shoup()", "const_ratio()", "nwt_2d_radix8_forward_inplace"]:
+        assert name in src, name
