@@ -23,6 +23,7 @@ SIGNATURES = {
     "b200fhe_primes_create": (i32, [u64, C.POINTER(i32), i32, U64P]),
     "b200fhe_min_primitive_root": (i32, [u64, u64, U64P]),
     "b200fhe_host_tables": (i32, [i32, u64, U64P, U64P, U64P, U64P, U64P, U64P]),
+    "b200fhe_host_tables_psi": (i32, [i32, u64, u64, U64P, U64P, U64P, U64P, U64P, U64P]),
     "b200fhe_const_ratio": (i32, [u64, U64P]),
     "b200fhe_ctx_create": (i32, [i32, U64P, i32, i32, C.POINTER(vp)]),
     "b200fhe_ctx_create_empty": (i32, [i32, i32, i32, C.POINTER(vp)]),
@@ -115,6 +116,25 @@ class Context:
         h = vp()
         check(lib().b200fhe_ctx_create(log_n, _p(arr), self.L, device, C.byref(h)))
         self._h = h
+
+    @classmethod
+    def from_psi(cls, log_n, moduli, psis, device=0):
+        """Context whose limb i uses the caller's primitive 2N-th root psis[i] instead of the minimal
+        one (DNTTTable::init + set with caller-built tables, reliability_test/ntt_test.cu:57-68)."""
+        self = cls.__new__(cls)
+        self.log_n, self.N = log_n, 1 << log_n
+        self.moduli = [int(q) for q in moduli]
+        self.L = len(self.moduli)
+        self.device = device
+        h = vp()
+        check(lib().b200fhe_ctx_create_empty(log_n, self.L, device, C.byref(h)))
+        self._h = h
+        for i, (q, psi) in enumerate(zip(self.moduli, psis)):
+            arrs = [np.zeros(self.N, dtype=np.uint64) for _ in range(4)]
+            ni, nis = u64(0), u64(0)
+            check(lib().b200fhe_host_tables_psi(log_n, q, int(psi), *[_p(a) for a in arrs], C.byref(ni), C.byref(nis)))
+            check(lib().b200fhe_ctx_set_tables(h, i, q, *[_p(a) for a in arrs], ni.value, nis.value, None))
+        return self
 
     def close(self):
         if getattr(self, "_h", None):

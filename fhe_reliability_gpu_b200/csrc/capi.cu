@@ -52,6 +52,19 @@ extern "C" int b200fhe_host_tables(int log_n, uint64_t q, uint64_t* rp, uint64_t
     if (n_inv_shoup) *n_inv_shoup = nt::shoup(ni, q);
     return 0;
 }
+extern "C" int b200fhe_host_tables_psi(int log_n, uint64_t q, uint64_t psi, uint64_t* rp, uint64_t* rps, uint64_t* irp,
+                                       uint64_t* irps, uint64_t* n_inv, uint64_t* n_inv_shoup) {
+    if (log_n < 1 || log_n > 20) return b200_set_err(B200FHE_EINVAL, "log_n out of range");
+    if (q < 3 || (q >> 60) || psi == 0 || psi >= q) return b200_set_err(B200FHE_EINVAL, "bad modulus or root");
+    uint64_t t = psi;
+    for (int i = 0; i < log_n; i++) t = nt::mulmod(t, t, q);          // psi^N must be -1
+    if (t != q - 1) return b200_set_err(B200FHE_EINVAL, "psi=%llu is not a primitive 2N-th root mod %llu", (unsigned long long)psi, (unsigned long long)q);
+    nt::tables(log_n, q, psi, rp, rps, irp, irps);
+    uint64_t ni = nt::invmod(((uint64_t)1 << log_n) % q, q);
+    if (n_inv) *n_inv = ni;
+    if (n_inv_shoup) *n_inv_shoup = nt::shoup(ni, q);
+    return 0;
+}
 extern "C" int b200fhe_const_ratio(uint64_t q, uint64_t ratio[2]) {
     if (q < 2 || !ratio) return b200_set_err(B200FHE_EINVAL, "bad modulus");
     nt::const_ratio(q, ratio);

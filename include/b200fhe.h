@@ -52,6 +52,11 @@ int b200fhe_min_primitive_root(uint64_t N, uint64_t q, uint64_t* psi);
 int b200fhe_host_tables(int log_n, uint64_t q, uint64_t* rp, uint64_t* rp_shoup, uint64_t* irp,
                         uint64_t* irp_shoup, uint64_t* n_inv, uint64_t* n_inv_shoup);
 
+/* Same tables for a caller-chosen primitive 2N-th root psi, as the Python prototypes take it
+ * (rfhe_framewk/src/negaclic_ntt.py:86 negacyclic_ntt(a, psi, mod)).  Fails if psi^N != -1. */
+int b200fhe_host_tables_psi(int log_n, uint64_t q, uint64_t psi, uint64_t* rp, uint64_t* rp_shoup, uint64_t* irp,
+                            uint64_t* irp_shoup, uint64_t* n_inv, uint64_t* n_inv_shoup);
+
 /* Modulus::const_ratio() (ntt_test.cu:51-52): floor(2^128/q) as two words. */
 int b200fhe_const_ratio(uint64_t q, uint64_t ratio[2]);
 
