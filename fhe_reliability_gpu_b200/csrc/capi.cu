@@ -90,6 +90,10 @@ static B200Mod make_mod(uint64_t q, int log_n, uint64_t itw1, uint64_t n_inv) {
     m.mprec = m.big ? (uint32_t)((((nt::u128)1) << (m.bits + 31)) / q) : 0;
     m.pshift = m.big ? m.bits - 33 : 0;
     m.q3 = 3 * q;
+    const uint64_t delta = m.bits < 64 ? ((uint64_t)1 << m.bits) - q : 0;
+    m.near = m.big && m.bits >= 40 && delta < ((uint64_t)1 << 31) &&
+             ((nt::u128)delta << (64 - m.bits)) < (q >> 1);
+    m.delta = m.near ? (uint32_t)delta : 0;
     (void)log_n;
     return m;
 }
@@ -281,12 +285,15 @@ static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, siz
     if (!c || (!d && n_poly && L)) return b200_set_err(B200FHE_EINVAL, "nwt: null argument");
     if (L == 0 || n_poly == 0) return 0;
     if (start + L > (size_t)c->L) return b200_set_err(B200FHE_EINVAL, "nwt: start_mod %zu + L %zu exceeds context (%d)", start, L, c->L);
-    bool big = true;
+    bool all_big = true, all_near = true;
     for (size_t i = start; i < start + L; i++) {
         if (!c->moduli[i]) return b200_set_err(B200FHE_EINVAL, "nwt: modulus %zu not set", i);
         if (inverse && !c->has_inverse[i]) return b200_set_err(B200FHE_EINVAL, "nwt: no inverse tables for modulus %zu", i);
-        big = big && c->h_mods[i].big;
+        all_big = all_big && c->h_mods[i].big;
+        all_near = all_near && c->h_mods[i].near;
     }
+    static const bool no_near = getenv("B200FHE_NO_NEAR") != nullptr;     // A/B switch for the NEAR kernels
+    const int big = (all_near && !no_near) ? 2 : all_big ? 1 : 0;
     CK(cudaSetDevice(c->device));
     PassArgs a;
     a.mods = c->d_mods;
@@ -455,8 +462,12 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
         h[i].payload = plan[i].payload;
     }
     if (n_plan) CK(cudaMemcpyAsync(c->d_inj, h, sizeof(InjEntry) * n_plan, cudaMemcpyHostToDevice, s));
-    bool big = true;
-    for (size_t i = start; i < start + L; i++) big = big && c->h_mods[i].big;
+    bool all_big = true, all_near = true;
+    for (size_t i = start; i < start + L; i++) {
+        all_big = all_big && c->h_mods[i].big;
+        all_near = all_near && c->h_mods[i].near;
+    }
+    const int big = (all_near && !getenv("B200FHE_NO_NEAR")) ? 2 : all_big ? 1 : 0;
     PassArgs a;
     a.mods = c->d_mods;
     a.tw = c->d_tw;

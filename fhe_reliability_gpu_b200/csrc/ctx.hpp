@@ -29,6 +29,7 @@ struct PassArgs {
     u32 N;
     u32 L;                    // limbs per polynomial in this call
     u32 start_mod;
+    u32 n_poly = 1;           // polynomials in this launch (grid.x = tiles * n_poly)
     // protected (ABFT) forward transform only
     const u64* omega = nullptr;     // [ctx.L][N] output weights, 30-bit halves packed (lo | hi << 32)
     u64* abft = nullptr;            // [n_limbs of the call][2][4] digit-sum counters
@@ -38,9 +39,10 @@ struct PassArgs {
 };
 
 // mask: 1 = first pass only, 2 = second pass only, 3 = whole transform
-int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s);
+// mode: 0 = any modulus, 1 = q >= 2^36 (BIG), 2 = q = 2^bits - delta (NEAR)
+int launch_ntt(bool inverse, int big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s);
 // protected forward transform (a.omega / a.abft set); counters must be zero on entry
-int launch_ntt_protected(bool big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s);
+int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s);
 // verdict[i] = (input checksum != output checksum); sums (optional) [n][2]; zeroes the counters
 void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s);
 

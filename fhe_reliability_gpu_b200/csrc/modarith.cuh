@@ -32,7 +32,8 @@ struct __align__(16) B200Mod {
     u32 bits;     // bit length of q
     u32 pshift;   // bits - 33: floor(v/q) ~ umulhi(v >> 32, mprec) >> pshift
     u64 q3;       // 3q, kept in memory so ptxas cannot rematerialise it as an IMAD.WIDE (multiplier pipe)
-    u64 pad_;
+    u32 delta;    // 2^bits - q when that fits 31 bits (pseudo-Mersenne shape of SEAL's top primes)
+    u32 near;     // 1 if the NEAR fast paths are valid: q = 2^bits - delta, delta * 2^(64-bits) < q/2
 };
 
 __device__ __forceinline__ u64 pack64(u32 lo, u32 hi) {
@@ -75,7 +76,12 @@ __device__ __forceinline__ u64 shoup_mul(u64 y, u64 w, u64 ws, u64 nq) {
 // cycles per warp, IMAD for 2: profiles/r1d_pipe_calibration.md).  Both cross terms use
 // mad.wide with a zero-extended 32-bit addend, which cannot overflow 64 bits, so no carry
 // chain is needed: s2 = yh*sl + lo32(yl*sh), k = yh*sh + hi32(yl*sh) + hi32(s2).
-__device__ __forceinline__ u64 shoup_mul_lazy(u64 y, u64 w, u64 ws, u64 nq) {
+//
+// MODE 2 (NEAR: q = 2^bits - delta with delta < 2^31, the shape of every prime CoeffModulus::Create
+// hands out): 2^64 - q = (2^32 - 2^sh) 2^32 + delta with sh = bits - 32, so the kl * hi32(-q) term of
+// the remainder is just -(kl << sh): one multiplier-pipe IMAD becomes a shift on the ALU pipe.
+template <int MODE = 1>
+__device__ __forceinline__ u64 shoup_mul_lazy(u64 y, u64 w, u64 ws, u64 nq, u32 nsh = 0) {
     u32 yl, yh, wl, wh, sl, sh, nl, nh, c1l, c1h, kl, kh, rl, rh;
     unpack64(y, yl, yh);
     unpack64(w, wl, wh);
@@ -93,16 +99,30 @@ __device__ __forceinline__ u64 shoup_mul_lazy(u64 y, u64 w, u64 ws, u64 nq) {
     unpack64(r, rl, rh);
     asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(yl), "r"(wh));
     asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(yh), "r"(wl));
-    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kl), "r"(nh));
+    if (MODE == 2) rh -= kl << nsh;
+    else asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kl), "r"(nh));
     asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kh), "r"(nl));
     return pack64(rl, rh);
 }
 
 // v (any 64-bit) -> congruent value < 2q when BIG (q >= 2^36: 32-bit normalised
 // reciprocal, quotient estimate off by at most one), < 3q otherwise.
-template <bool BIG>
+// NEAR: v = k 2^bits + r  ->  r + k delta  (= v - k q), one IMAD.WIDE; < 2^bits + 2^(64-bits) delta < 2q.
+template <int BIG>
 __device__ __forceinline__ u64 reduce_lazy(u64 v, const B200Mod& m) {
-    if (BIG) {
+#ifdef B200_ABL_NOREDUCE     // timing ablation only (wrong results)
+    return v;
+#endif
+    if (BIG == 2) {
+        u32 vl, vh;
+        unpack64(v, vl, vh);
+        const u32 sh = m.bits - 32;
+        const u32 k = vh >> sh;
+        const u64 low = pack64(vl, vh & ((1u << sh) - 1u));
+        u64 r;
+        asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(k), "r"(m.delta), "l"(low));
+        return r;
+    } else if (BIG) {
         u32 vl, vh, nl, nh, rl, rh;
         unpack64(v, vl, vh);
         unpack64(0 - m.q, nl, nh);
@@ -119,17 +139,25 @@ __device__ __forceinline__ u64 reduce_lazy(u64 v, const B200Mod& m) {
     }
 }
 // bound (in units of q) of reduce_lazy's result
-template <bool BIG> struct LazyBound { static constexpr int value = BIG ? 2 : 3; };
+template <int BIG> struct LazyBound { static constexpr int value = BIG ? 2 : 3; };
 
 // v < 3q -> [0,q)
 __device__ __forceinline__ u64 canon3(u64 v, u64 q) {
+#ifdef B200_ABL_NOCANON
+    return v;
+#endif
     u64 two_q = q << 1;
     if (v >= two_q) v -= two_q;
     if (v >= q) v -= q;
     return v;
 }
 // v < 2q -> [0,q)
-__device__ __forceinline__ u64 canon2(u64 v, u64 q) { return v >= q ? v - q : v; }
+__device__ __forceinline__ u64 canon2(u64 v, u64 q) {
+#ifdef B200_ABL_NOCANON
+    return v;
+#endif
+    return v >= q ? v - q : v;
+}
 
 // full a*b mod q, a,b < 2^64 with a*b < q*2^64 is NOT required: generic 128-bit
 // Barrett with the two-word ratio (SEAL barrett_reduce_128).  Result in [0,q).

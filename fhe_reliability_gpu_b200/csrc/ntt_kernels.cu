@@ -54,22 +54,31 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 // ---------------------------------------------------------------- forward, columns
 // PROT: the protected transform (config C4) -- accumulates the input side of the
 // ABFT checksum while the coefficients are loaded and honours the injection plan.
-template <int LC, int LA, bool BIG, bool PROT, bool INJ>
+template <int LC, int LA, int BIG, bool PROT, bool INJ>
 __global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
 k_fwd_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
     extern __shared__ u64 sm[];
-    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
+    // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
+    const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
+    const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
     const B200Mod m = p.mods[mi];
     const ulonglong2* tw = p.tw + (size_t)mi * p.N;
-    u64* base = p.data + (size_t)limb * p.N + blockIdx.x * kTile;
+    u64* base = p.data + (size_t)limb * p.N + tile * kTile;
     const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
-    const u32 col = blockIdx.x * kTile + c;
+    const u32 col = tile * kTile + c;
     u64 ck0 = 0, ck1 = 0;
+    // the 2^LC - 1 twiddles of the column stages are shared by every thread of the CTA: stage them once
+    ulonglong2* stw = reinterpret_cast<ulonglong2*>(sm + (LB > 0 ? (kTile << LC) : 0));
+    u64 v[RA];
     if (g < RB) {
-        u64 v[RA];
 #pragma unroll
         for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
+    }
+    for (int i = threadIdx.x; i < (1 << LC); i += blockDim.x) stw[i] = __ldg(tw + i);
+    __syncthreads();
+    if (g < RB) {
         if constexpr (PROT) {
             AbftIn acc;
             const int pl = (LC + kRowLog + 1) / 2;
@@ -78,10 +87,10 @@ k_fwd_col(PassArgs p) {
             acc.value(ck0, ck1);
         }
         if constexpr (INJ)
-            ct_phase<LA, BIG>(v, TwGlobal{tw, 1u}, m,
+            ct_phase<LA, BIG>(v, TwShared{stw, 1u}, m,
                               Inject{p.inj, p.n_inj, p.limb0 + limb, (u32)g * kRowLen + col, (u32)(LB + kRowLog), 0u, m.q});
         else
-            ct_phase<LA, BIG>(v, TwGlobal{tw, 1u}, m);
+            ct_phase<LA, BIG>(v, TwShared{stw, 1u}, m);
         if (LB > 0) {
 #pragma unroll
             for (int e = 0; e < RA; e++) sm[(e * RB + g) * kTile + c] = v[e];
@@ -98,10 +107,10 @@ k_fwd_col(PassArgs p) {
 #pragma unroll
             for (int e = 0; e < RB; e++) w[e] = sm[(g * RB + e) * kTile + c];
             if constexpr (INJ)
-                ct_phase<LB, BIG>(w, TwGlobal{tw, (1u << LA) + g}, m,
+                ct_phase<LB, BIG>(w, TwShared{stw, (1u << LA) + g}, m,
                                   Inject{p.inj, p.n_inj, p.limb0 + limb, (u32)(g * RB) * kRowLen + col, (u32)kRowLog, (u32)LA, m.q});
             else
-                ct_phase<LB, BIG>(w, TwGlobal{tw, (1u << LA) + g}, m);
+                ct_phase<LB, BIG>(w, TwShared{stw, (1u << LA) + g}, m);
 #pragma unroll
             for (int e = 0; e < RB; e++) base[(size_t)(g * RB + e) * kRowLen + c] = w[e];
         }
@@ -125,25 +134,36 @@ struct RowSmem {
 constexpr u32 kRowTileBytes = sizeof(ulonglong2) * kRowTileEntries;
 constexpr int kRowCtasPerSm = (220 * 1024) / (int)sizeof(RowSmem) > 16 ? 16 : (220 * 1024) / (int)sizeof(RowSmem);
 
-template <bool BIG, bool PROT, bool INJ>
+template <int BIG, bool PROT, bool INJ>
 __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
     RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
-    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
+    // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
+    const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
+    const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
     const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
+#ifndef B200_ABL_NOTMA
     if (threadIdx.x == 0) {
         mbar_init(&s.bar, 1);
         mbar_expect_tx(&s.bar, kRowTileBytes);
-        bulk_g2s(s.twA, p.rtw + (size_t)mi * p.N + (size_t)blockIdx.x * (kRowTileBytes / 16), kRowTileBytes, &s.bar);
+        bulk_g2s(s.twA, p.rtw + (size_t)mi * p.N + (size_t)tile * (kRowTileBytes / 16), kRowTileBytes, &s.bar);
     }
+#endif
     const B200Mod m = p.mods[mi];
-    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(blockIdx.x * kRowsPerCta + rl) * kRowLen;
+    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
 #pragma unroll
+#ifdef B200_ABL_NOLOAD
+    for (int e = 0; e < 16; e++) v[e] = (u64)threadIdx.x * 0x9E3779B97F4A7C15ull + e + (u64)rowp;
+#else
     for (int e = 0; e < 16; e++) v[e] = rowp[e * 16 + cl];
+#endif
+#ifndef B200_ABL_NOTMA
     __syncthreads();                     // barrier initialised before anyone polls it
     mbar_wait(&s.bar, 0);
-    const u32 x0 = (blockIdx.x * kRowsPerCta + rl) * kRowLen;     // first coefficient of the row
+#endif
+    const u32 x0 = (tile * kRowsPerCta + rl) * kRowLen;     // first coefficient of the row
     const u32 lc = 31 - __clz(p.N >> kRowLog);                     // stages done by the column pass
     if constexpr (INJ) ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m, Inject{p.inj, p.n_inj, p.limb0 + limb, x0 + cl, 4u, lc, m.q});
     else ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m);
@@ -183,7 +203,11 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
     for (int e = 0; e < 16; e++) v[e] = BIG ? canon2(reduce_lazy<BIG>(v[e], m), m.q) : canon3(reduce_lazy<BIG>(v[e], m), m.q);
     ulonglong2* out = reinterpret_cast<ulonglong2*>(rowp + cl * 16);
 #pragma unroll
+#ifdef B200_ABL_NOSTORE
+    { u64 acc = 0; for (int e = 0; e < 16; e++) acc ^= v[e]; if (acc == 0x1234567) out[0] = make_ulonglong2(acc, acc); }
+#else
     for (int e = 0; e < 8; e++) out[e] = make_ulonglong2(v[2 * e], v[2 * e + 1]);
+#endif
     if constexpr (PROT) {
         // output side of the checksum, on the values just stored
         asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -201,19 +225,22 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
     }
 }
 
-template <bool BIG>
+template <int BIG>
 __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
     RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
-    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
+    // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
+    const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
+    const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
     const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
     if (threadIdx.x == 0) {
         mbar_init(&s.bar, 1);
         mbar_expect_tx(&s.bar, kRowTileBytes);
-        bulk_g2s(s.twA, p.rtw + (size_t)mi * p.N + (size_t)blockIdx.x * (kRowTileBytes / 16), kRowTileBytes, &s.bar);
+        bulk_g2s(s.twA, p.rtw + (size_t)mi * p.N + (size_t)tile * (kRowTileBytes / 16), kRowTileBytes, &s.bar);
     }
     const B200Mod m = p.mods[mi];
-    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(blockIdx.x * kRowsPerCta + rl) * kRowLen;
+    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
     const ulonglong2* in = reinterpret_cast<const ulonglong2*>(rowp + cl * 16);
 #pragma unroll
@@ -240,22 +267,31 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs
 }
 
 // ---------------------------------------------------------------- inverse, columns
-template <int LC, int LA, bool BIG>
+template <int LC, int LA, int BIG>
 __global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
 k_inv_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
     extern __shared__ u64 sm[];
-    const u32 limb = blockIdx.y, mi = p.start_mod + limb % p.L;
+    // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
+    // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
+    const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
+    const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
     const B200Mod m = p.mods[mi];
     const ulonglong2* itw = p.tw + (size_t)mi * p.N;
-    u64* base = p.data + (size_t)limb * p.N + blockIdx.x * kTile;
+    u64* base = p.data + (size_t)limb * p.N + tile * kTile;
     const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
+    ulonglong2* stw = reinterpret_cast<ulonglong2*>(sm + (LB > 0 ? (kTile << LC) : 0));
+    for (int i = threadIdx.x; i < (1 << LC); i += blockDim.x) stw[i] = __ldg(itw + i);
+    if constexpr (LB == 0) __syncthreads();
     if constexpr (LB > 0) {
+        u64 w[RB];
         if (g < RA) {
-            u64 w[RB];
 #pragma unroll
             for (int e = 0; e < RB; e++) w[e] = base[(size_t)(g * RB + e) * kRowLen + c];
-            gs_phase<LB, BIG, false>(w, TwGlobal{itw, (1u << LA) + g}, m);
+        }
+        __syncthreads();
+        if (g < RA) {
+            gs_phase<LB, BIG, false>(w, TwShared{stw, (1u << LA) + g}, m);
 #pragma unroll
             for (int e = 0; e < RB; e++) sm[(g * RB + e) * kTile + c] = w[e];
         }
@@ -270,7 +306,7 @@ k_inv_col(PassArgs p) {
 #pragma unroll
             for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
         }
-        gs_phase<LA, BIG, true>(v, TwGlobal{itw, 1u}, m);
+        gs_phase<LA, BIG, true>(v, TwShared{stw, 1u}, m);
 #pragma unroll
         for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
     }
@@ -355,11 +391,14 @@ __global__ void k_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 s
 }
 
 // ---------------------------------------------------------------- dispatch
-template <int LC, int LA, bool BIG, bool PROT = false, bool INJ = false>
-static void launch_fwd2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
+template <int LC, int LA, int BIG, bool PROT = false, bool INJ = false>
+static void launch_fwd2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
-    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kRowsPerCta, n_limbs);
-    constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
+    const u32 np = n_limbs / a_in.L;
+    PassArgs a = a_in;
+    a.n_poly = np;
+    dim3 gc((kRowLen / kTile) * np, a.L), gr(((a.N >> kRowLog) / kRowsPerCta) * np, a.L);
+    constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (mask & 1) k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
     if (mask & 2) {
@@ -367,20 +406,23 @@ static void launch_fwd2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s
         k_fwd_row<BIG, PROT, INJ><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
     }
 }
-template <int LC, int LA, bool BIG>
-static void launch_inv2(const PassArgs& a, u32 n_limbs, int mask, cudaStream_t s) {
+template <int LC, int LA, int BIG>
+static void launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
-    dim3 gc(kRowLen / kTile, n_limbs), gr((a.N >> kRowLog) / kRowsPerCta, n_limbs);
+    const u32 np = n_limbs / a_in.L;
+    PassArgs a = a_in;
+    a.n_poly = np;
+    dim3 gc((kRowLen / kTile) * np, a.L), gr(((a.N >> kRowLog) / kRowsPerCta) * np, a.L);
     if (mask & 1) {
         cudaFuncSetAttribute(k_inv_row<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
         k_inv_row<BIG><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
     }
-    constexpr size_t smem = LB > 0 ? sizeof(u64) * (kTile << LC) : 0;
+    constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_inv_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (mask & 2) k_inv_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
 }
 
-template <bool BIG>
+template <int BIG>
 static int launch_ntt_t(bool inverse, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
 #define B200_CASE(LOGN, LC, LA)                                              \
     case LOGN:                                                               \
@@ -388,12 +430,14 @@ static int launch_ntt_t(bool inverse, const PassArgs& a, int logn, u32 n_limbs, 
         else launch_fwd2<LC, LA, BIG>(a, n_limbs, mask, s);                        \
         return 0;
     switch (logn) {
+#ifndef B200_FAST_BUILD      // experiment builds instantiate the N = 2^16 kernels only
         B200_CASE(12, 4, 4)
         B200_CASE(13, 5, 3)
         B200_CASE(14, 6, 3)
         B200_CASE(15, 7, 4)
-        B200_CASE(16, 8, 4)
         B200_CASE(17, 9, 5)
+#endif
+        B200_CASE(16, 8, 4)
     }
 #undef B200_CASE
     return -1;
@@ -401,7 +445,7 @@ static int launch_ntt_t(bool inverse, const PassArgs& a, int logn, u32 n_limbs, 
 
 // Launch the transform on n_limbs limbs ([n_poly][L][N], limb l of each poly
 // uses modulus start_mod + l).  Returns 0, or <0 if logn is unsupported.
-int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
+int launch_ntt(bool inverse, int big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
     if (n_limbs == 0) return 0;
     if (logn >= 1 && logn <= 11) {
         size_t smem = sizeof(u64) << logn;
@@ -417,34 +461,48 @@ int launch_ntt(bool inverse, bool big, const PassArgs& a, int logn, u32 n_limbs,
         // keep limb->modulus mapping: off must be a multiple of L
         u32 cnt = n_limbs - off < kMaxY ? n_limbs - off : kMaxY;
         if (off % a.L) return -2;
-        int rc = big ? launch_ntt_t<true>(inverse, b, logn, cnt, mask, s) : launch_ntt_t<false>(inverse, b, logn, cnt, mask, s);
+#ifdef B200_FAST_BUILD
+        int rc = big == 2 ? launch_ntt_t<2>(inverse, b, logn, cnt, mask, s) : big ? launch_ntt_t<1>(inverse, b, logn, cnt, mask, s) : -3;
+#else
+        int rc = big == 2 ? launch_ntt_t<2>(inverse, b, logn, cnt, mask, s)
+                 : big  ? launch_ntt_t<1>(inverse, b, logn, cnt, mask, s) : launch_ntt_t<0>(inverse, b, logn, cnt, mask, s);
+#endif
         if (rc) return rc;
     }
     return 0;
 }
 
-template <bool BIG, bool INJ>
+template <int BIG, bool INJ>
 static int launch_prot_t(const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
     switch (logn) {
+#ifndef B200_FAST_BUILD
         case 12: launch_fwd2<4, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
         case 13: launch_fwd2<5, 3, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
         case 14: launch_fwd2<6, 3, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
         case 15: launch_fwd2<7, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
-        case 16: launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
         case 17: launch_fwd2<9, 5, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+#endif
+        case 16: launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
     }
     return -1;
 }
 
-int launch_ntt_protected(bool big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
     if (n_limbs == 0) return 0;
     if (n_limbs > 32768) return -2;
     if (logn >= 1 && logn <= 11) {
         k_small<false, true><<<n_limbs, 256, sizeof(u64) << logn, s>>>(a, logn);
         return 0;
     }
-    if (a.n_inj) return big ? launch_prot_t<true, true>(a, logn, n_limbs, s) : launch_prot_t<false, true>(a, logn, n_limbs, s);
-    return big ? launch_prot_t<true, false>(a, logn, n_limbs, s) : launch_prot_t<false, false>(a, logn, n_limbs, s);
+#ifdef B200_FAST_BUILD
+    if (!big || a.n_inj) return -3;
+    return big == 2 ? launch_prot_t<2, false>(a, logn, n_limbs, s) : launch_prot_t<1, false>(a, logn, n_limbs, s);
+#else
+    // the injection variants exist for the general modes only: NEAR moduli are also valid BIG moduli
+    if (a.n_inj) return big ? launch_prot_t<1, true>(a, logn, n_limbs, s) : launch_prot_t<0, true>(a, logn, n_limbs, s);
+    return big == 2 ? launch_prot_t<2, false>(a, logn, n_limbs, s)
+           : big   ? launch_prot_t<1, false>(a, logn, n_limbs, s) : launch_prot_t<0, false>(a, logn, n_limbs, s);
+#endif
 }
 
 void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s) {

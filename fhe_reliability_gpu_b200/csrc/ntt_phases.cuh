@@ -23,11 +23,25 @@ struct TwGlobal {
     u32 Pp;
     __device__ __forceinline__ ulonglong2 get(int t, int g) const { return __ldg(tw + ((Pp << t) + g)); }
 };
+// the same indexing from a copy of the table's first entries staged in shared memory (column passes)
+struct TwShared {
+    const ulonglong2* tw;
+    u32 Pp;
+#ifdef B200_ABL_TWREG
+    __device__ __forceinline__ ulonglong2 get(int t, int g) const { return tw[Pp]; }
+#else
+    __device__ __forceinline__ ulonglong2 get(int t, int g) const { return tw[(Pp << t) + g]; }
+#endif
+};
 // entry j = (1 << t) - 1 + g of a per-thread (or per-row) list with a fixed stride (shared memory)
 template <int STRIDE>
 struct TwList {
     const ulonglong2* base;
+#ifdef B200_ABL_TWREG
+    __device__ __forceinline__ ulonglong2 get(int t, int g) const { return base[0]; }
+#else
     __device__ __forceinline__ ulonglong2 get(int t, int g) const { return base[((1 << t) - 1 + g) * STRIDE]; }
+#endif
 };
 
 // ---- fault-injection hook (protected path only) ---------------------------------------------
@@ -66,10 +80,14 @@ struct Inject {
 // residues).  Out: values < 16q.  Lazy products are < 3q, so the X path grows by 3q per
 // sub-stage from reduce_lazy's bound B0 <= 3: 15q after four sub-stages; a fifth
 // sub-stage (LR = 5, the N = 2^17 column pass) re-reduces its X inputs first.
-template <int LR, bool BIG, class TW, class INJ = NoInject>
+template <int LR, int BIG, class TW, class INJ = NoInject>
 __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m, const INJ& inj = INJ()) {
     constexpr int R = 1 << LR;
+#ifdef B200_ABL_NOCOMPUTE     // timing ablation: memory side only
+    if (m.q != 12345) return;
+#endif
     const u64 q = m.q, q3 = m.q3, nq = 0 - q;
+    const u32 sh = m.bits - 32;            // NEAR only
 #pragma unroll
     for (int e = 0; e < R / 2; e++) v[e] = reduce_lazy<BIG>(v[e], m);   // X half of sub-stage 0
 #pragma unroll
@@ -86,7 +104,7 @@ __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const 
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int a = g * 2 * half + i, b = a + half;
-                u64 T = shoup_mul_lazy(v[b], W.x, W.y, nq);
+                u64 T = shoup_mul_lazy<BIG>(v[b], W.x, W.y, nq, sh);
                 if (INJ::on) T = inj.apply(t, a, T);
                 const u64 X = v[a];
                 v[a] = X + T;
@@ -99,10 +117,14 @@ __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const 
 // Inverse Gentleman-Sande phase.  In: any 64-bit words.  Out: lazily reduced
 // values (< 16q) unless LAST, in which case the final sub-stage (global stage 0)
 // folds N^-1 in and the outputs are canonical [0,q).
-template <int LR, bool BIG, bool LAST, class TW>
+template <int LR, int BIG, bool LAST, class TW>
 __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m) {
     constexpr int R = 1 << LR;
+#ifdef B200_ABL_NOCOMPUTE
+    if (m.q != 12345) return;
+#endif
     const u64 q = m.q, nq = 0 - q;
+    const u32 sh = m.bits - 32;            // NEAR only
 #pragma unroll
     for (int e = 0; e < R; e++) v[e] = reduce_lazy<BIG>(v[e], m);
     int bound = LazyBound<BIG>::value;                                  // compile-time after unroll
@@ -130,8 +152,8 @@ __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const 
                 const int a = g * 2 * half + i, b = a + half;
                 const u64 U = v[a], V = v[b];
                 const u64 S = U + V;
-                v[b] = shoup_mul_lazy(U - V + bq, W.x, W.y, nq);
-                v[a] = fold ? shoup_mul_lazy(S, m.ninv, m.ninv_s, nq) : S;
+                v[b] = shoup_mul_lazy<BIG>(U - V + bq, W.x, W.y, nq, sh);
+                v[a] = fold ? shoup_mul_lazy<BIG>(S, m.ninv, m.ninv_s, nq, sh) : S;
             }
         }
         bound *= 2;
