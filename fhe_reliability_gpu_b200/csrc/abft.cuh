@@ -14,7 +14,7 @@
 // 64-bit sums; omega_k and the canonical outputs are split at 30 bits so the four
 // partial products of 16 coefficients fit 64-bit sums.  One Barrett reduction
 // partial products of 16 coefficients fit 64-bit sums.  The per-thread sums are committed
-// unreduced (20-bit digits, one REDUX + one atomic per digit per warp); the single modular
+// unreduced (26-bit digits, one REDUX + one RED per digit per warp); the single modular
 // reduction per limb happens in k_abft_finalize.
 #pragma once
 #include "modarith.cuh"
@@ -57,21 +57,24 @@ struct AbftOut {
 };
 
 // counters: [limb][side][8] u64, side 0 = input sum, 1 = output sum.  The 128-bit per-thread sum
-// (s1:s0) is committed unreduced as NDIG 20-bit digits: one REDUX per digit and one atomic per digit
+// (s1:s0) is committed unreduced as NDIG 26-bit digits: one REDUX per digit and one atomic per digit
 // per warp; k_abft_finalize recombines the digit sums and reduces mod q once per limb.
 constexpr int kAbftStride = 8;
+constexpr int kAbftDigit = 26;       // 32 lanes x 26-bit digits sum to < 2^31: one 32-bit REDUX per digit
 template <int NDIG>
 __device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u64 s0, u64 s1) {
     u64* c = counters + ((size_t)limb * 2 + side) * kAbftStride;
+    constexpr u32 mask = (1u << kAbftDigit) - 1u;
 #pragma unroll
     for (int d = 0; d < NDIG; d++) {
-        const int sh = 20 * d;
+        const int sh = kAbftDigit * d;
         u32 dig;
-        if (sh + 20 <= 64) dig = (u32)(s0 >> sh) & 0xfffffu;
-        else if (sh >= 64) dig = (u32)(s1 >> (sh - 64)) & 0xfffffu;
-        else dig = (u32)((s0 >> sh) | (s1 << (64 - sh))) & 0xfffffu;
-        const u32 sum = __reduce_add_sync(0xffffffffu, dig);
-        if ((threadIdx.x & 31) == 0) atomicAdd(reinterpret_cast<unsigned long long*>(c + d), (unsigned long long)sum);
+        if (sh + kAbftDigit <= 64) dig = (u32)(s0 >> sh) & mask;
+        else if (sh >= 64) dig = (u32)(s1 >> (sh - 64)) & mask;
+        else dig = (u32)((s0 >> sh) | (s1 << (64 - sh))) & mask;
+        const u64 sum = __reduce_add_sync(0xffffffffu, dig);
+        // plain RED from lane 0 (inline PTX: atomicAdd here makes nvcc emit its warp-aggregation sequence per digit)
+        if ((threadIdx.x & 31) == 0) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(c + d), "l"(sum) : "memory");
     }
 }
 

@@ -99,7 +99,7 @@ k_fwd_col(PassArgs p) {
             for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
         }
     }
-    if constexpr (PROT) abft_commit<5>(p.abft, p.limb0 + limb, 0, ck0, ck1);
+    if constexpr (PROT) abft_commit<4>(p.abft, p.limb0 + limb, 0, ck0, ck1);
     if constexpr (LB > 0) {
         __syncthreads();
         if (g < RA) {
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
         }
         u64 s0, s1;
         acc.value(s0, s1);
-        abft_commit<7>(p.abft, p.limb0 + limb, 1, s0, s1);
+        abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1);
     }
 }
 
@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
         if (PROT) ain.add(abft_w(i, (logn + 1) / 2), x);
         a[i] = canon3(reduce_lazy<false>(x, m), m.q);
     }
-    if (PROT) { u64 s0, s1; ain.value(s0, s1); abft_commit<5>(p.abft, p.limb0 + limb, 0, s0, s1); }
+    if (PROT) { u64 s0, s1; ain.value(s0, s1); abft_commit<4>(p.abft, p.limb0 + limb, 0, s0, s1); }
     __syncthreads();
     if (!INVERSE) {
         for (int s = 0; s < logn; s++) {
@@ -368,26 +368,30 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
         base[i] = a[i];
         if (PROT) aout.add(p.omega[(size_t)mi * N + i], a[i]);
     }
-    if (PROT) { u64 s0, s1; aout.value(s0, s1); abft_commit<7>(p.abft, p.limb0 + limb, 1, s0, s1); }
+    if (PROT) { u64 s0, s1; aout.value(s0, s1); abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1); }
 }
 
-// one thread per limb: compare the two checksums, publish verdict and sums, clear the counters
+// one thread per (limb, side): recombine the digit sums (Horner, Barrett per step) and clear the counters;
+// the even lane of each pair compares the two sides and publishes verdict and sums
 __global__ void k_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums) {
-    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_limbs) return;
-    const u64 q = mods[start_mod + i % L].q;
-    u64 val[2];
-    for (int side = 0; side < 2; side++) {
+    const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+    const u32 i = t >> 1, side = t & 1;
+    u64 r = 0;
+    if (i < n_limbs) {
+        const B200Mod m = mods[start_mod + i % L];
         u64* c = counters + ((size_t)i * 2 + side) * kAbftStride;
-        u64 r = 0;                                   // Horner over the 20-bit digit sums, top digit first
-        for (int d = kAbftStride - 1; d >= 0; d--) {
-            r = (u64)((((unsigned __int128)r << 20) + c[d]) % q);
+        for (int d = kAbftStride - 1; d >= 0; d--) {   // r < q < 2^60: (r << 26) + c[d] < q 2^64
+            const u64 lo = (r << kAbftDigit) + c[d];
+            const u64 hi = (r >> (64 - kAbftDigit)) + (lo < c[d]);
+            r = barrett128(lo, hi, m);
             c[d] = 0;
         }
-        val[side] = r;
     }
-    if (verdict) verdict[i] = val[0] != val[1];
-    if (sums) { sums[2 * i] = val[0]; sums[2 * i + 1] = val[1]; }
+    const u64 other = __shfl_xor_sync(0xffffffffu, r, 1);
+    if (i < n_limbs && side == 0) {
+        if (verdict) verdict[i] = r != other;
+        if (sums) { sums[2 * i] = r; sums[2 * i + 1] = other; }
+    }
 }
 
 // ---------------------------------------------------------------- dispatch
@@ -506,7 +510,7 @@ int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cuda
 }
 
 void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s) {
-    if (n_limbs) k_abft_finalize<<<(n_limbs + 127) / 128, 128, 0, s>>>(counters, mods, L, start_mod, n_limbs, verdict, sums);
+    if (n_limbs) k_abft_finalize<<<(2 * n_limbs + 127) / 128, 128, 0, s>>>(counters, mods, L, start_mod, n_limbs, verdict, sums);
 }
 
 }  // namespace b200

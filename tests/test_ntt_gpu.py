@@ -121,3 +121,71 @@ def test_error_paths(pkg):
         ctx.nwt_forward_host(a, L=3, start_mod=0)   # exceeds context
     # empty batch is a no-op
     assert pkg.lib().b200fhe_nwt_forward(ctx._h, None, 0, 2, 0, None) == 0
+
+
+def _is_prime(n):
+    if n < 2:
+        return False
+    for p in (2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37):
+        if n % p == 0:
+            return n == p
+    d, s = n - 1, 0
+    while d % 2 == 0:
+        d //= 2; s += 1
+    for a in (2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37):
+        x = pow(a, d, n)
+        if x in (1, n - 1):
+            continue
+        for _ in range(s - 1):
+            x = x * x % n
+            if x == n - 1:
+                break
+        else:
+            return False
+    return True
+
+
+def _primes_far_from_a_power_of_two(N, start, count):
+    out, k = [], start // (2 * N)
+    while len(out) < count:
+        if _is_prime(k * 2 * N + 1):
+            out.append(k * 2 * N + 1)
+        k -= 1
+    return out
+
+
+@pytest.mark.parametrize("log_n", [12, 14, 16, 17])
+def test_general_moduli_take_the_non_pseudo_mersenne_kernels(pkg, O, log_n):
+    """CoeffModulus::Create only yields primes just below 2^bits, which run the NEAR kernels
+    (q = 2^bits - delta).  Arbitrary NTT primes (anywhere below 2^60, e.g. the special primes of a
+    key-switching basis) must run the general kernels: alone, and mixed with NEAR primes in one call."""
+    N = 1 << log_n
+    far = _primes_far_from_a_power_of_two(N, int(0.71 * 2 ** 60), 2) + _primes_far_from_a_power_of_two(N, int(0.6 * 2 ** 47), 1)
+    near = pkg.primes_create(N, [60])
+    for moduli in (far, far[:2] + near):
+        ctx = pkg.Context(log_n, moduli)
+        a = O.uniform_limbs(moduli, N, seed=77 + log_n)
+        tabs = [O.Tables(log_n, q) for q in moduli]
+        got = ctx.nwt_forward_host(a.copy())
+        assert np.array_equal(got, O.ntt_forward_batch(a, tabs))
+        assert np.array_equal(ctx.nwt_backward_host(got.copy()), a)
+        wild = np.random.default_rng(log_n).integers(0, 2 ** 64, size=a.shape, dtype=np.uint64)
+        assert np.array_equal(ctx.nwt_forward_host(wild.copy()), O.ntt_forward_batch(wild, tabs))
+        _, verdict, sums = ctx.nwt_forward_protected_host(a.copy())
+        assert not verdict.any() and (sums[:, 0] == sums[:, 1]).all()
+
+
+def test_many_polys_share_twiddle_tiles(pkg, O):
+    """The grid runs the polynomials of a batch back to back per modulus (L2 reuse of the twiddle
+    tile): 5 polys x 3 limbs at N=2^16, every limb against the oracle."""
+    log_n, L, n_poly = 16, 3, 5
+    ctx, moduli = _ctx(pkg, log_n, 60, L)
+    N = 1 << log_n
+    tabs = [O.Tables(log_n, q) for q in moduli]
+    a = np.stack([O.uniform_limbs(moduli, N, seed=300 + i) for i in range(n_poly)])
+    want = np.stack([O.ntt_forward_batch(a[i], tabs) for i in range(n_poly)])
+    got = ctx.nwt_forward_host(a.copy())
+    assert np.array_equal(got, want)
+    assert np.array_equal(ctx.nwt_backward_host(got.copy()), a)
+    _, verdict, _ = ctx.nwt_forward_protected_host(a.copy())
+    assert not verdict.any()
