@@ -55,6 +55,9 @@ def cpu_reference(steps, warmup, sample_polys=1):
             O.ntt_inverse_batch(a[i], tabs, inplace=True)
     for _ in range(warmup):
         step()
+    if steps is None:                       # size the sample to about 10 s of CPU work
+        t0 = time.perf_counter(); step(); one = time.perf_counter() - t0
+        steps = int(min(2000, max(5, 10.0 / max(one, 1e-6))))
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
@@ -232,11 +235,20 @@ def main():
     # one pass kernel = half of a limb-transform's 16 B/coeff (the pair shares the 1 MiB)
     algo_bytes_launch = npoly * L * ALGO_BYTES_PER_LIMB_TRANSFORM / 2
     ach = algo_bytes_launch / (kern[dom] * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+    # dram__bytes_read.sum + dram__bytes_write.sum per whole-batch launch, from the committed ncu --set full capture of this
+    # same command (profiles/r1f_ncu_full_summary.txt; npoly=8): MB read + MB written
+    NCU_TRAFFIC = {"k_fwd_col": (151.18 + 91.23) * 1e6, "k_fwd_row": (188.78 + 98.55) * 1e6,
+                   "k_inv_row": (188.78 + 93.93) * 1e6, "k_inv_col": (151.18 + 91.21) * 1e6}
+    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": NCU_TRAFFIC[dom] if npoly == NPOLY else None,
+            "traffic_source": "profiles/r1f_ncu_full_summary.txt (ncu --set full, same command, per launch)",
             "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes_launch,
-            "kernel_ms": kern, "note": "standalone whole-batch pass: intermediate not L2-resident (worst case); "
-            "transform_frac = limb-transforms/s x 1 MiB / peak",
-            "transform_frac": value / world * ALGO_BYTES_PER_LIMB_TRANSFORM / 1e9 / peak}
+            "kernel_ms": kern, "note": "one pass kernel over the whole batch = half of a transform's 16 B/coeff; "
+            "transform_frac = limb-transforms/s x 1 MiB / peak.  The kernels are bound by the integer-multiply pipe "
+            "(sm__pipe_fmaheavy 70-76 % busy in the same capture), not by HBM: DESIGN.md section 6",
+            "transform_frac": value / world * ALGO_BYTES_PER_LIMB_TRANSFORM / 1e9 / peak,
+            "integer_pipe": {"fmaheavy_busy_pct_ncu": {"k_fwd_col": 75.9, "k_fwd_row": 70.0, "k_inv_row": 71.5, "k_inv_col": 75.0},
+                             "ceiling_limb_transforms_per_s_at_100pct": 2.73e6}}
 
     # e2e: host buffers through the C ABI (H2D + kernels + D2H per call)
     hp = hv.ctypes.data_as(C.POINTER(C.c_uint64))
@@ -268,7 +280,7 @@ def main():
                        "steps": e2e_steps, "timer": "host perf_counter around synchronous C-ABI calls, max over ranks"},
                "roofline": roof, "abft": abft}
         if world == 1 and not args.no_cpu_baseline:
-            v, ms, cores, sample = cpu_reference(10, 1)
+            v, ms, cores, sample = cpu_reference(None, 1)      # about 10 s of host work
             out["cpu_baseline"] = {"value": v, "unit": "limb-transforms/s", "cores": cores, "kind": "port", "sample": sample}
         print(json.dumps(out))
     if world > 1:
