@@ -38,6 +38,7 @@ SIGNATURES = {
     "b200fhe_nwt_forward_protected": (i32, [vp, vp, sz, sz, sz, vp, vp, vp, sz, vp]),
     "b200fhe_nwt_forward_protected_host": (i32, [vp, U64P, sz, sz, sz, C.POINTER(C.c_uint32), U64P, vp, sz]),
     "b200fhe_abft_weights": (i32, [vp, i32, U64P, U64P]),
+    "b200fhe_four_step_protected_host": (i32, [u64, u64, sz, U64P, U64P, sz, U64P, C.POINTER(C.c_uint32), vp, sz, i32]),
     "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_bconv_create": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, C.POINTER(vp)]),
@@ -264,3 +265,24 @@ class BaseConv:
 
 def flip_bit(ptr, idx, bit, stream=0):
     check(lib().b200fhe_flip_bit(ptr, idx, bit, stream))
+
+
+class FsInject(C.Structure):
+    """b200fhe_fs_inject: `vector[row] += delta` after matrix stage 1 or 2 (four_step_ntt_prot.py:271-274)."""
+    _fields_ = [("transform", C.c_uint32), ("stage", C.c_uint32), ("row", C.c_uint64), ("delta", C.c_uint64)]
+
+
+def four_step_protected_host(a, mod, g, plan=(), device=0):
+    """a [batch][N] uint64 -> (y [batch][N], checks [batch][4] = lhs1, rhs1, lhs2, rhs2, verdict [batch])."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    batch, N = a.shape
+    y = np.zeros_like(a)
+    checks = np.zeros((batch, 4), dtype=np.uint64)
+    verdict = np.zeros(batch, dtype=np.uint32)
+    plan = list(plan)
+    arr = (FsInject * max(len(plan), 1))()
+    for i, (tr, stage, row, delta) in enumerate(plan):
+        arr[i] = FsInject(tr, stage, row, delta)
+    check(lib().b200fhe_four_step_protected_host(mod, g, N, _p(a), _p(y), batch, _p(checks),
+                                                 verdict.ctypes.data_as(C.POINTER(C.c_uint32)), C.cast(arr, vp), len(plan), device))
+    return y, checks, verdict

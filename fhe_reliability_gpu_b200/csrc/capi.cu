@@ -72,7 +72,7 @@ extern "C" int b200fhe_const_ratio(uint64_t q, uint64_t ratio[2]) {
 }
 
 // ---------------------------------------------------------------- context
-static B200Mod make_mod(uint64_t q, int log_n, uint64_t itw1, uint64_t n_inv) {
+B200Mod b200_make_mod(uint64_t q, uint64_t itw1, uint64_t n_inv) {
     B200Mod m;
     memset(&m, 0, sizeof(m));
     m.q = q;
@@ -94,7 +94,6 @@ static B200Mod make_mod(uint64_t q, int log_n, uint64_t itw1, uint64_t n_inv) {
     m.near = m.big && m.bits >= 40 && delta < ((uint64_t)1 << 31) &&
              ((nt::u128)delta << (64 - m.bits)) < (q >> 1);
     m.delta = m.near ? (uint32_t)delta : 0;
-    (void)log_n;
     return m;
 }
 
@@ -191,7 +190,7 @@ extern "C" int b200fhe_ctx_set_tables(b200fhe_ctx* c, int idx, uint64_t q, const
     c->moduli[idx] = q;
     c->psi[idx] = N > 1 ? tw[N >> 1] : 1;   // root_powers[bitrev(1)] = psi
     c->has_omega[idx] = 0;
-    c->h_mods[idx] = make_mod(q, c->log_n, itw1, n_inv);
+    c->h_mods[idx] = b200_make_mod(q, itw1, n_inv);
     CK(cudaMemcpyAsync(c->d_mods + idx, &c->h_mods[idx], sizeof(B200Mod), cudaMemcpyHostToDevice, s));
     CK(cudaStreamSynchronize(s));
     return 0;

@@ -167,3 +167,19 @@ def ecc_check(a, psi, mod, plan=()):
     c = _ctx(n, psi, mod)
     _, verdict, sums = c.nwt_forward_protected_host(_arr(a, mod).reshape(1, 1, n), plan=plan)
     return int(sums[0, 0]), int(sums[0, 1]), not bool(verdict[0])
+
+
+def four_step_with_protection_vector(a, N, mod=MOD, g=G, fault=None):
+    """reliability_test/four_step_ntt_prot.py:196-252: returns (y, checks) with
+    checks = {"stage1": {lhs, rhs, ok}, "stage2": {...}, "y_matches_reference": bool}, every number
+    produced by the literal four-step kernel (b200fhe_four_step_protected_host).  `fault` =
+    (stage, row, delta) adds delta to one entry of that stage's output, as demo() does (:271-274)."""
+    if len(a) != N:
+        raise ValueError("len(a) != N")
+    plan = [(0, fault[0], fault[1], fault[2])] if fault else []
+    y, chk, _ = B.four_step_protected_host(_arr(a, mod).reshape(1, N), mod, g, plan=plan)
+    y = [int(v) for v in y[0]]
+    l1, r1, l2, r2 = (int(v) for v in chk[0])
+    checks = {"stage1": {"lhs": l1, "rhs": r1, "ok": l1 == r1}, "stage2": {"lhs": l2, "rhs": r2, "ok": l2 == r2},
+              "y_matches_reference": y == four_step_ntt(a, N, mod, g)}
+    return y, checks

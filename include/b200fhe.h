@@ -149,6 +149,28 @@ int b200fhe_nwt_forward_protected_host(b200fhe_ctx* ctx, uint64_t* h_inout, size
  * output order); either pointer may be NULL. */
 int b200fhe_abft_weights(b200fhe_ctx* ctx, int idx, uint64_t* w, uint64_t* w_hat);
 
+/* ---- the prototype's protected four-step NTT, literally (reliability_test/four_step_ntt_prot.py) ---- */
+
+/* One fault added to an intermediate vector, as demo() does (four_step_ntt_prot.py:271-274:
+ * C1_fault[i] = C1[i] + delta after the stage-1 matrix multiply): stage 1 or 2, row = index into that
+ * stage's output vector in the prototype's layout. */
+typedef struct b200fhe_fs_inject {
+    uint32_t transform;  /* which transform of the batch */
+    uint32_t stage;      /* 1 or 2 */
+    uint64_t row;
+    uint64_t delta;
+} b200fhe_fs_inject;
+
+/* four_step_with_protection_vector(a, N, mod, g) (four_step_ntt_prot.py:196-252) for `batch` vectors:
+ * cyclic NTT y_k = sum_t a_t w^(kt), w = g^((mod-1)/N), N = n*n <= 4096, computed as the prototype's
+ * factorisation Pi_k (I x W_n) S D (I x W_n) Pi_t with its protection equality
+ * sum(C) == colsum(A) . rowsum(B) (:185-194) evaluated on both matrix stages in the same kernel.
+ * h_checks[t] = {lhs1, rhs1, lhs2, rhs2}; h_verdict[t] bit 0 / bit 1 = stage 1 / stage 2 check failed.
+ * Host buffers in and out (the prototype's lists). */
+int b200fhe_four_step_protected_host(uint64_t mod, uint64_t g, size_t N, const uint64_t* h_in, uint64_t* h_out, size_t batch,
+                                     uint64_t* h_checks, uint32_t* h_verdict, const b200fhe_fs_inject* plan, size_t n_plan,
+                                     int device);
+
 /* ---- ct x pt multiply-accumulate (config C3) ------------------------------- */
 
 /* out[p][l][i] = sum_{k<n_terms} ct_k[p][l][i] * pt_k[l][i] mod q_{start_mod+l}, NTT domain.

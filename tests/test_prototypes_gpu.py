@@ -62,3 +62,42 @@ def test_bad_arguments_raise(pkg):
         P.negacyclic_ntt([1, 2, 3], 19, 97)                      # not a power of two
     with pytest.raises(Exception):
         P.negacyclic_ntt([1] * 16, 5, 97)                        # 5 is not a primitive 32nd root mod 97
+
+
+def test_literal_four_step_protection_checks_match_prototype(pkg):
+    """four_step_with_protection_vector (four_step_ntt_prot.py:196-252): y and both (lhs, rhs) pairs equal the
+    prototype's own numbers, including demo(16, seed=42): stage1 527369946, stage2 4580965."""
+    from fhe_reliability_gpu_b200 import prototypes as P
+    g = load("four_step_prot.json")
+    n = 0
+    for c in g["cases"]:
+        y, checks = P.four_step_with_protection_vector(c["a"], c["N"], c["mod"], c["g"])
+        assert y == c["y"] and checks["y_matches_reference"]
+        if "checks" in c:
+            n += 1
+            for st in ("stage1", "stage2"):
+                assert checks[st]["lhs"] == c["checks"][st]["lhs"] and checks[st]["rhs"] == c["checks"][st]["rhs"] and checks[st]["ok"]
+    assert n >= 1
+    d16 = [c for c in g["cases"] if c["N"] == 16 and c["seed"] == 42][0]
+    y, checks = P.four_step_with_protection_vector(d16["a"], 16)
+    assert (checks["stage1"]["lhs"], checks["stage2"]["lhs"]) == (527369946, 4580965)
+    # the demo's fault (:271-279): row 13 of the stage-1 output, +34126397 -> lhs 561496343, rhs unchanged, detected
+    f = g["demo_fault"]
+    y, checks = P.four_step_with_protection_vector(d16["a"], 16, fault=(1, f["row"], f["delta"]))
+    assert checks["stage1"] == {"lhs": 561496343, "rhs": 527369946, "ok": False}
+    assert not checks["y_matches_reference"]
+
+
+def test_literal_four_step_batch_sizes_and_stage2_fault(pkg):
+    import numpy as np
+    from fhe_reliability_gpu_b200 import binding as B, prototypes as P
+    mod, gen = 998244353, 3
+    rng = np.random.default_rng(4)
+    for N in (4, 64, 1024, 4096):
+        a = rng.integers(0, mod, size=(3, N), dtype=np.uint64)
+        y, chk, verdict = B.four_step_protected_host(a, mod, gen, plan=[(1, 2, N - 1, 5)])
+        assert verdict.tolist() == [0, 2, 0]
+        assert (chk[:, 0] == chk[:, 1]).all() and chk[0, 2] == chk[0, 3] and chk[1, 2] != chk[1, 3]
+        assert [int(v) for v in y[0]] == P.ntt([int(v) for v in a[0]], pow(gen, (mod - 1) // N, mod), mod)
+    with pytest.raises(B.B200FHEError):
+        B.four_step_protected_host(np.zeros((1, 32), dtype=np.uint64), mod, gen)      # not a perfect square
