@@ -271,14 +271,6 @@ static size_t chunk_polys(const b200fhe_ctx* c, size_t L) {
     if (n > cap) n = cap;
     return n ? n : 1;
 }
-// Polynomials per pipeline stage of the host-buffer path: 40 MiB pieces keep H2D, kernels and D2H
-// of neighbouring pieces overlapped on the three streams.
-static size_t host_chunk_polys(const b200fhe_ctx* c, size_t L) {
-    const size_t bytes_per_poly = L * c->N * sizeof(uint64_t);
-    size_t n = ((size_t)40 << 20) / (bytes_per_poly ? bytes_per_poly : 1);
-    return n ? n : 1;
-}
-
 static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, size_t L, size_t start, int mask,
                    cudaStream_t s) {
     if (!c || (!d && n_poly && L)) return b200_set_err(B200FHE_EINVAL, "nwt: null argument");
@@ -376,8 +368,27 @@ static int run_ntt_host(b200fhe_ctx* c, bool inverse, uint64_t* h, size_t n_poly
         CK(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
     }
-    const size_t step = host_chunk_polys(c, L);
-    const size_t n_chunks = (n_poly + step - 1) / step;
+    // pipeline pieces: whole polynomials when they are small, limb ranges of one polynomial otherwise.  The first
+    // H2D and the last D2H of a call cannot overlap anything, so pieces are kept near 16 MiB
+    // (B200FHE_HOST_CHUNK_MB; sweep 2/4/8/16/36 MiB -> 58/65/74/79/74 k limb-transforms/s end to end).
+    struct Piece { size_t off, np, L, start; };
+    std::vector<Piece> pieces;
+    static const size_t target = [] {
+        const char* e = getenv("B200FHE_HOST_CHUNK_MB");
+        return (size_t)(e && atoi(e) > 0 ? atoi(e) : 16) << 20;
+    }();
+    const size_t limb_bytes = c->N * sizeof(uint64_t), poly_bytes = L * limb_bytes;
+    if (poly_bytes <= target) {
+        const size_t step = target / poly_bytes;
+        for (size_t p0 = 0; p0 < n_poly; p0 += step)
+            pieces.push_back({p0 * poly_words, n_poly - p0 < step ? n_poly - p0 : step, L, start});
+    } else {
+        const size_t lc = target / limb_bytes ? target / limb_bytes : 1;
+        for (size_t p0 = 0; p0 < n_poly; p0++)
+            for (size_t l0 = 0; l0 < L; l0 += lc)
+                pieces.push_back({p0 * poly_words + l0 * c->N, 1, L - l0 < lc ? L - l0 : lc, start + l0});
+    }
+    const size_t n_chunks = pieces.size();
     if (c->ev.size() < 2 * n_chunks) {
         size_t old = c->ev.size();
         c->ev.resize(2 * n_chunks);
@@ -385,12 +396,12 @@ static int run_ntt_host(b200fhe_ctx* c, bool inverse, uint64_t* h, size_t n_poly
     }
     cudaStream_t sk = c->own_stream;
     for (size_t k = 0; k < n_chunks; k++) {
-        const size_t p0 = k * step, np = n_poly - p0 < step ? n_poly - p0 : step;
-        const size_t off = p0 * poly_words, cnt = np * poly_words;
+        const Piece& pc = pieces[k];
+        const size_t off = pc.off, cnt = pc.np * pc.L * c->N;
         CK(cudaMemcpyAsync(c->d_stage + off, src + off, cnt * sizeof(uint64_t), cudaMemcpyHostToDevice, c->s_h2d));
         CK(cudaEventRecord(c->ev[2 * k], c->s_h2d));
         CK(cudaStreamWaitEvent(sk, c->ev[2 * k], 0));
-        rc = run_ntt(c, inverse, c->d_stage + off, np, L, start, 3, sk);
+        rc = run_ntt(c, inverse, c->d_stage + off, pc.np, pc.L, pc.start, 3, sk);
         if (rc) return rc;
         CK(cudaEventRecord(c->ev[2 * k + 1], sk));
         CK(cudaStreamWaitEvent(c->s_d2h, c->ev[2 * k + 1], 0));
