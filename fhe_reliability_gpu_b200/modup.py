@@ -97,7 +97,15 @@ class CudaBackend:
         return self.convs[key]
 
     def empty(self, n_limbs):
-        return self.torch.zeros((n_limbs, self.N), dtype=self.torch.int64, device=self.device)
+        # every row that is read later is written first (padding rows of a gather are skipped by gathered_rows)
+        return self.torch.empty((n_limbs, self.N), dtype=self.torch.int64, device=self.device)
+
+    def stack(self, limbs, rows):
+        """[rows][N] buffer whose first len(limbs) rows are the given limbs: one copy kernel instead of one per limb."""
+        x = self.empty(rows)
+        if limbs:
+            self.torch.stack(limbs, out=x[:len(limbs)])
+        return x
 
     def _runs(self, limb_ids):
         runs, i = [], 0
@@ -151,9 +159,12 @@ def modup_digit(plan, backend, dist, d, my_limbs):
     conv = backend.conv((d, plan.rank), src, mine_t) if mine_t else None
     sconv = conv if conv is not None else backend.conv((d, plan.rank, "s"), src, src[:1])
     # 1-2: inverse NTT and scaling of the owned digit limbs (one contiguous run of the source order)
-    x = backend.empty(max(cmax, 1))
-    for i, g in enumerate(mine_d):
-        x[i] = my_limbs[g]
+    if hasattr(backend, "stack"):
+        x = backend.stack([my_limbs[g] for g in mine_d], max(cmax, 1))
+    else:
+        x = backend.empty(max(cmax, 1))
+        for i, g in enumerate(mine_d):
+            x[i] = my_limbs[g]
     backend.intt(x[:len(mine_d)], mine_d)
     y = backend.empty(max(cmax, 1))
     backend.scale(sconv, x, y, src.index(mine_d[0]) if mine_d else 0, len(mine_d))
