@@ -47,6 +47,12 @@ SIGNATURES = {
     "b200fhe_bconv_contract": (i32, [vp, vp, vp, sz, sz, vp]),
     "b200fhe_bconv_modup": (i32, [vp, vp, vp, vp]),
     "b200fhe_bconv_modup_host": (i32, [vp, U64P, U64P]),
+    "b200fhe_keyswitch_create": (i32, [vp, i32, i32, i32, C.POINTER(vp)]),
+    "b200fhe_keyswitch_destroy": (i32, [vp]),
+    "b200fhe_keyswitch_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(sz)]),
+    "b200fhe_keyswitch_modup": (i32, [vp, vp, vp, vp]),
+    "b200fhe_keyswitch_moddown": (i32, [vp, vp, vp, vp, sz, vp]),
+    "b200fhe_keyswitch_apply": (i32, [vp, vp, vp, vp, vp, vp]),
     "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
     "b200fhe_host_alloc": (i32, [C.POINTER(vp), sz]),
     "b200fhe_host_free": (i32, [vp]),
@@ -261,6 +267,38 @@ class BaseConv:
         out = np.zeros((self.K, self.N), dtype=np.uint64)
         check(lib().b200fhe_bconv_modup_host(self._h, _p(x), _p(out)))
         return out
+
+
+class KeySwitch:
+    """Hybrid key-switch plan (b200fhe_keyswitch): ctx holds n_q ciphertext moduli then n_p special primes.
+    Device pointers in and out (torch tensors' data_ptr()); shapes in include/b200fhe.h."""
+
+    def __init__(self, ctx, n_q, n_p, dnum):
+        self.ctx, self.n_q, self.n_p, self.dnum, self.N = ctx, n_q, n_p, dnum, ctx.N
+        h = vp()
+        check(lib().b200fhe_keyswitch_create(ctx._h, n_q, n_p, dnum, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200fhe_keyswitch_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def workspace_bytes(self):
+        w = sz()
+        check(lib().b200fhe_keyswitch_info(self._h, None, None, None, C.byref(w)))
+        return int(w.value)
+
+    def modup(self, c_ptr, up_ptr, stream=0):
+        check(lib().b200fhe_keyswitch_modup(self._h, c_ptr, up_ptr, stream))
+
+    def moddown(self, acc_q_ptr, acc_p_ptr, out_ptr, n_poly, stream=0):
+        check(lib().b200fhe_keyswitch_moddown(self._h, acc_q_ptr, acc_p_ptr, out_ptr, n_poly, stream))
+
+    def apply(self, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, stream=0):
+        check(lib().b200fhe_keyswitch_apply(self._h, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, stream))
 
 
 def flip_bit(ptr, idx, bit, stream=0):

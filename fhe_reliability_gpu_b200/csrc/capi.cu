@@ -255,6 +255,7 @@ extern "C" int b200fhe_ctx_moduli(const b200fhe_ctx* c, uint64_t* out) {
 // ---------------------------------------------------------------- transforms
 static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py's gpu_launches)
 extern "C" unsigned long long b200fhe_launch_count(void) { return g_launches; }
+void b200_count_launches(unsigned n) { g_launches += n; }
 
 // Polynomials per launch on the device-resident path.  The transform is bound by the integer
 // multiplier pipe, not by HBM (profiles/r1e_*), so keeping the lazily-reduced intermediate inside

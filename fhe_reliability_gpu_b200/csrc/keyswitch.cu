@@ -1,0 +1,228 @@
+// Hybrid key-switch: the step relinearize_inplace / rotate_inplace spend their time in
+// (call sites reliability_test/dotprod_test.cu:114,146; SEAL switch_key_inplace, callgrind.out.ckks:11081;
+// NTT 48 % + base conversion 42 % of it at dnum = 3, profile_framewk/draw_dnum.py:5-9):
+//
+//   c  [n_q][N]  (NTT domain, moduli q_0..q_{n_q-1})
+//   1. x = INTT(c)                                       one batched launch over all digits
+//   2. per digit d (limbs [d a, (d+1) a)):  y_d = x_d (D_d/q_j)^-1 mod q_j            (k_bconv_scale)
+//      up_d[targets] = NTT( sum_j y_dj (D_d/q_j) mod target )                          (k_bconv_contract + NTT)
+//      up_d[digit limbs] = c[digit limbs]                                              (pass through)
+//   3. acc[p] = sum_d up_d (.) evk_d[p],  p = 0,1, over all n_q + n_p limbs             (k_pmult, T = dnum)
+//   4. ModDown: t = INTT(acc[p] mod P);  conv = NTT( BaseConv_{P->Q}(t) );
+//      out[p] = (acc[p] - conv) P^-1 mod q_l                                           (k_moddown_combine)
+//
+// The context must hold the moduli in the order q_0..q_{n_q-1}, p_0..p_{n_p-1}.  evk is stored split into its Q and P
+// limb ranges ([dnum][2][n_q][N] and [dnum][2][n_p][N]) so each range is one pmult launch.  Both base conversions are the
+// HPS fast conversion (b200fhe_bconv): ModDown's result differs from the exact floor((acc - [acc]_P)/P) by at most n_p,
+// the usual approximate-ModDown noise.  All work is enqueued on the caller's stream; nothing synchronises or allocates
+// after create, so the whole switch can be captured in a CUDA graph.
+#include "../../include/b200fhe.h"
+#include "ctx.hpp"
+#include "numth.hpp"
+#include <vector>
+
+using namespace b200;
+
+int b200_set_err(int code, const char* fmt, ...);
+void b200_count_launches(unsigned n);
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return b200_set_err(B200FHE_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                __FILE__, __LINE__);                                               \
+    } while (0)
+#define RC(call)            \
+    do {                    \
+        int rc_ = (call);   \
+        if (rc_) return rc_; \
+    } while (0)
+
+struct b200fhe_keyswitch {
+    b200fhe_ctx* ctx = nullptr;
+    int n_q = 0, n_p = 0, dnum = 0, alpha = 0;
+    std::vector<b200fhe_bconv*> up;      // per digit: digit limbs -> every other limb of Q u P
+    b200fhe_bconv* down = nullptr;       // P -> Q
+    ulonglong2* d_pinv = nullptr;        // [n_q] (P^-1 mod q_l, Shoup quotient)
+    uint64_t* d_ws = nullptr;                 // workspace, see offsets
+    size_t o_x = 0, o_y = 0, o_up = 0, o_accq = 0, o_accp = 0, o_conv = 0, ws_words = 0;
+};
+
+namespace b200 {
+
+// out[p][l][i] = (acc[p][l][i] - conv[p][l][i]) * Pinv_l mod q_l; one thread = two coefficients
+__global__ void __launch_bounds__(256) k_moddown_combine(const u64* __restrict__ acc, const u64* __restrict__ conv, u64* __restrict__ out,
+                                                         const B200Mod* mods, const ulonglong2* pinv, u32 N, u32 L) {
+    const u32 limb = blockIdx.y;
+    const u64 q = mods[limb].q;
+    const ulonglong2 w = pinv[limb];
+    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i2 * 2 >= N) return;
+    const size_t off = (((size_t)blockIdx.z * L + limb) * N) / 2 + i2;
+    const ulonglong2 a = __ldcs(reinterpret_cast<const ulonglong2*>(acc) + off);
+    const ulonglong2 b = __ldcs(reinterpret_cast<const ulonglong2*>(conv) + off);
+    const u64 nq = 0 - q;
+    // inputs are canonical (pmult and the forward NTT both end in [0,q))
+    const u64 dx = a.x - b.x + (a.x < b.x ? q : 0), dy = a.y - b.y + (a.y < b.y ? q : 0);
+    ulonglong2 r;
+    r.x = canon2(shoup_mul(dx, w.x, w.y, nq), q);
+    r.y = canon2(shoup_mul(dy, w.x, w.y, nq), q);
+    reinterpret_cast<ulonglong2*>(out)[off] = r;
+}
+
+}  // namespace b200
+
+extern "C" int b200fhe_keyswitch_destroy(b200fhe_keyswitch* k) {
+    if (!k) return 0;
+    if (k->ctx) cudaSetDevice(k->ctx->device);
+    for (b200fhe_bconv* p : k->up) b200fhe_bconv_destroy(p);
+    b200fhe_bconv_destroy(k->down);
+    if (k->d_pinv) cudaFree(k->d_pinv);
+    if (k->d_ws) cudaFree(k->d_ws);
+    delete k;
+    return 0;
+}
+
+extern "C" int b200fhe_keyswitch_create(b200fhe_ctx* c, int n_q, int n_p, int dnum, b200fhe_keyswitch** out) {
+    if (!c || !out || n_q < 1 || n_p < 1 || dnum < 1) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: bad arguments");
+    if (n_q + n_p != c->L) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: context holds %d moduli, need n_q + n_p = %d", c->L, n_q + n_p);
+    if (n_q % dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: n_q=%d not divisible by dnum=%d", n_q, dnum);
+    if (c->N < 2) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: N too small");
+    for (int i = 0; i < c->L; i++)
+        if (!c->moduli[i] || !c->has_inverse[i]) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: modulus %d has no inverse tables", i);
+    const int alpha = n_q / dnum, total = n_q + n_p;
+    if (alpha > 64 || n_p > 64) return b200_set_err(B200FHE_EUNSUPPORTED, "keyswitch_create: digit or special base larger than 64 limbs");
+    b200fhe_keyswitch* k = new b200fhe_keyswitch();
+    k->ctx = c; k->n_q = n_q; k->n_p = n_p; k->dnum = dnum; k->alpha = alpha;
+    int rc = 0;
+    for (int d = 0; d < dnum && !rc; d++) {
+        std::vector<int> src, dst;
+        for (int g = d * alpha; g < (d + 1) * alpha; g++) src.push_back(g);
+        for (int g = 0; g < total; g++)
+            if (g < d * alpha || g >= (d + 1) * alpha) dst.push_back(g);
+        b200fhe_bconv* p = nullptr;
+        rc = b200fhe_bconv_create(c, src.data(), alpha, dst.data(), (int)dst.size(), &p);
+        if (!rc) k->up.push_back(p);
+    }
+    if (!rc) {
+        std::vector<int> src, dst;
+        for (int g = n_q; g < total; g++) src.push_back(g);
+        for (int g = 0; g < n_q; g++) dst.push_back(g);
+        rc = b200fhe_bconv_create(c, src.data(), n_p, dst.data(), n_q, &k->down);
+    }
+    if (rc) {
+        b200fhe_keyswitch_destroy(k);
+        return rc;
+    }
+    std::vector<ulonglong2> pinv(n_q);
+    for (int l = 0; l < n_q; l++) {
+        const uint64_t q = c->moduli[l];
+        uint64_t P = 1;
+        for (int j = n_q; j < total; j++) P = nt::mulmod(P, c->moduli[j] % q, q);
+        const uint64_t iv = nt::invmod(P, q);
+        pinv[l] = make_ulonglong2(iv, nt::shoup(iv, q));
+    }
+    const size_t N = c->N;
+    size_t o = 0;
+    k->o_x = o;    o += (size_t)n_q * N;                 // INTT(c)
+    k->o_y = o;    o += (size_t)(n_q > 2 * n_p ? n_q : 2 * n_p) * N;   // scaled digits; reused for the scaled P part of ModDown
+    k->o_up = o;   o += (size_t)dnum * total * N;        // raised digits
+    k->o_accq = o; o += (size_t)2 * n_q * N;
+    k->o_accp = o; o += (size_t)2 * n_p * N;
+    k->o_conv = o; o += (size_t)2 * n_q * N;
+    k->ws_words = o;
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e == cudaSuccess) e = cudaMalloc(&k->d_pinv, sizeof(ulonglong2) * n_q);
+    if (e == cudaSuccess) e = cudaMalloc(&k->d_ws, sizeof(uint64_t) * o);
+    if (e == cudaSuccess) e = cudaMemcpy(k->d_pinv, pinv.data(), sizeof(ulonglong2) * n_q, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        b200fhe_keyswitch_destroy(k);
+        return b200_set_err(e == cudaErrorMemoryAllocation ? B200FHE_ENOMEM : B200FHE_ECUDA, "keyswitch_create: %s", cudaGetErrorString(e));
+    }
+    *out = k;
+    return 0;
+}
+
+// steps 1-2: every digit of c raised to the full basis, NTT domain.  d_up [dnum][n_q + n_p][N].
+extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, void* stream) {
+    if (!k || !d_c || !d_up) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: null argument");
+    b200fhe_ctx* c = k->ctx;
+    CK(cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t N = c->N, a = (size_t)k->alpha, total = (size_t)k->n_q + k->n_p;
+    uint64_t* x = k->d_ws + k->o_x;
+    uint64_t* y = k->d_ws + k->o_y;
+    CK(cudaMemcpyAsync(x, d_c, sizeof(uint64_t) * k->n_q * N, cudaMemcpyDeviceToDevice, s));
+    // the digit's own limbs pass through
+    for (int d = 0; d < k->dnum; d++)
+        CK(cudaMemcpyAsync(d_up + ((size_t)d * total + (size_t)d * a) * N, d_c + (size_t)d * a * N, sizeof(uint64_t) * a * N,
+                           cudaMemcpyDeviceToDevice, s));
+    RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
+    for (int d = 0; d < k->dnum; d++) {
+        b200fhe_bconv* p = k->up[d];
+        const uint64_t* xd = x + (size_t)d * a * N;
+        uint64_t* yd = y + (size_t)d * a * N;
+        uint64_t* upd = (uint64_t*)d_up + (size_t)d * total * N;
+        RC(b200fhe_bconv_scale(p, xd, yd, 0, a, stream));
+        const size_t below = (size_t)d * a, above = total - below - a;
+        RC(b200fhe_bconv_contract(p, yd, upd, 0, below, stream));
+        RC(b200fhe_bconv_contract(p, yd, upd + (below + a) * N, below, above, stream));
+        if (below) RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
+        RC(b200fhe_nwt_forward(c, upd + (below + a) * N, 1, above, below + a, stream));
+    }
+    return 0;
+}
+
+// step 4 for n_poly polynomials: d_acc_q [n_poly][n_q][N], d_acc_p [n_poly][n_p][N] (overwritten), d_out [n_poly][n_q][N]
+// (may alias d_acc_q).  n_poly <= 2.
+extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out,
+                                         size_t n_poly, void* stream) {
+    if (!k || !d_acc_q || !d_acc_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: null argument");
+    if (n_poly < 1 || n_poly > 2) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: n_poly must be 1 or 2");
+    b200fhe_ctx* c = k->ctx;
+    CK(cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t N = c->N, nq = (size_t)k->n_q, np = (size_t)k->n_p;
+    uint64_t* y = k->d_ws + k->o_y;
+    uint64_t* conv = k->d_ws + k->o_conv;
+    RC(b200fhe_nwt_backward(c, d_acc_p, n_poly, np, nq, stream));
+    for (size_t p = 0; p < n_poly; p++) {
+        RC(b200fhe_bconv_scale(k->down, d_acc_p + p * np * N, y + p * np * N, 0, np, stream));
+        RC(b200fhe_bconv_contract(k->down, y + p * np * N, conv + p * nq * N, 0, nq, stream));
+    }
+    RC(b200fhe_nwt_forward(c, conv, n_poly, nq, 0, stream));
+    dim3 grid((unsigned)((N / 2 + 255) / 256), (unsigned)nq, (unsigned)n_poly);
+    k_moddown_combine<<<grid, 256, 0, s>>>((const u64*)d_acc_q, (const u64*)conv, (u64*)d_out, c->d_mods, k->d_pinv, (u32)N, (u32)nq);
+    b200_count_launches(1);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// The whole switch: d_c [n_q][N]; d_evk_q [dnum][2][n_q][N]; d_evk_p [dnum][2][n_p][N]; d_out [2][n_q][N].
+// out[0] + out[1] s  ~  c s'   when evk_d = (-a_d s + e_d + P B_d s', a_d) with B_d the CRT basis element of digit d.
+extern "C" int b200fhe_keyswitch_apply(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                                       uint64_t* d_out, void* stream) {
+    if (!k || !d_c || !d_evk_q || !d_evk_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: null argument");
+    b200fhe_ctx* c = k->ctx;
+    const size_t N = c->N, nq = (size_t)k->n_q, np = (size_t)k->n_p, total = nq + np;
+    uint64_t* up = k->d_ws + k->o_up;
+    uint64_t* accq = k->d_ws + k->o_accq;
+    uint64_t* accp = k->d_ws + k->o_accp;
+    RC(b200fhe_keyswitch_modup(k, d_c, up, stream));
+    std::vector<const uint64_t*> ct(k->dnum), pt(k->dnum);
+    for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
+    RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accq, 2, nq, 0, 0, stream));
+    for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_p + (size_t)d * 2 * np * N; pt[d] = up + ((size_t)d * total + nq) * N; }
+    RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accp, 2, np, nq, 0, stream));
+    return b200fhe_keyswitch_moddown(k, accq, accp, d_out, 2, stream);
+}
+
+extern "C" int b200fhe_keyswitch_info(const b200fhe_keyswitch* k, int* n_q, int* n_p, int* dnum, size_t* workspace_bytes) {
+    if (!k) return b200_set_err(B200FHE_EINVAL, "keyswitch_info: null plan");
+    if (n_q) *n_q = k->n_q;
+    if (n_p) *n_p = k->n_p;
+    if (dnum) *dnum = k->dnum;
+    if (workspace_bytes) *workspace_bytes = k->ws_words * sizeof(uint64_t);
+    return 0;
+}

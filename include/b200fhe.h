@@ -213,6 +213,36 @@ int b200fhe_bconv_contract(b200fhe_bconv* plan, const uint64_t* d_y, uint64_t* d
 int b200fhe_bconv_modup(b200fhe_bconv* plan, const uint64_t* d_in, uint64_t* d_out, void* stream);
 int b200fhe_bconv_modup_host(b200fhe_bconv* plan, const uint64_t* h_in, uint64_t* h_out);
 
+/* ---- hybrid key-switch: ModUp -> evk inner product -> ModDown -------------------
+ * The work inside Phantom's relinearize_inplace / rotate_inplace (reliability_test/dotprod_test.cu:114,146)
+ * and SEAL's switch_key_inplace (callgrind.out.ckks:11081; cost split profile_framewk/draw_dnum.py:5-9).
+ * The context must hold n_q ciphertext moduli followed by n_p special primes, all with inverse tables;
+ * digits are the dnum runs of n_q/dnum consecutive ciphertext limbs.  Base conversions are the HPS fast
+ * conversion (b200fhe_bconv).  Every call only enqueues work on `stream` (no allocation, no
+ * synchronisation), so a switch can be captured in a CUDA graph. */
+typedef struct b200fhe_keyswitch b200fhe_keyswitch;
+int b200fhe_keyswitch_create(b200fhe_ctx* ctx, int n_q, int n_p, int dnum, b200fhe_keyswitch** out);
+int b200fhe_keyswitch_destroy(b200fhe_keyswitch* plan);
+int b200fhe_keyswitch_info(const b200fhe_keyswitch* plan, int* n_q, int* n_p, int* dnum, size_t* workspace_bytes);
+
+/* ModUp of every digit: d_c [n_q][N] (NTT domain) -> d_up [dnum][n_q + n_p][N] (NTT domain);
+ * up_d = the digit's residues raised to all n_q + n_p moduli, its own limbs copied through. */
+int b200fhe_keyswitch_modup(b200fhe_keyswitch* plan, const uint64_t* d_c, uint64_t* d_up, void* stream);
+
+/* ModDown of n_poly (1 or 2) polynomials given as their Q limbs d_acc_q [n_poly][n_q][N] and P limbs
+ * d_acc_p [n_poly][n_p][N] (NTT domain; d_acc_p is overwritten):
+ * d_out [n_poly][n_q][N] = (acc - BaseConv_{P->Q}(acc mod P)) * P^-1 mod q_l, NTT domain, in [0,q).
+ * d_out may alias d_acc_q. */
+int b200fhe_keyswitch_moddown(b200fhe_keyswitch* plan, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out,
+                              size_t n_poly, void* stream);
+
+/* The whole switch.  d_c [n_q][N]; the key d_evk_q [dnum][2][n_q][N], d_evk_p [dnum][2][n_p][N] (component
+ * 0 = b_d, 1 = a_d, split into the Q and P limb ranges); d_out [2][n_q][N] with
+ * out[0] + out[1] s = c s' + small noise  when  b_d = -a_d s + e_d + P B_d s'  (B_d = the CRT basis element
+ * of digit d: 1 modulo the digit's moduli, 0 modulo the other ciphertext moduli). */
+int b200fhe_keyswitch_apply(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                            uint64_t* d_out, void* stream);
+
 /* Measurement hooks (bench.py): one pass of the two-kernel transform
  * (pass 1 = first kernel, 2 = second), and the number of kernels this library
  * has launched in this process. */

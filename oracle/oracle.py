@@ -241,3 +241,46 @@ def uniform_limbs(moduli, N, seed=20250606):
     for l, q in enumerate(moduli):
         out[l] = rng.integers(0, int(q), size=N, dtype=np.uint64)
     return out
+
+
+# ---------------------------------------------------------------- hybrid key-switch
+def keyswitch_modup(c, moduli, n_q, n_p, dnum, tabs):
+    """ModUp of every digit (dotprod_test.cu:114,146 relinearize/rotate, SEAL switch_key_inplace; spec of the
+    conversion itself rfhe_framewk/src/baseConv.py:10-40 in its HPS form): c [n_q][N] NTT domain ->
+    [dnum][n_q+n_p][N] NTT domain, the digit's own limbs copied through.  Composed from the pinned primitives."""
+    c = np.ascontiguousarray(c, dtype=np.uint64)
+    N = c.shape[1]
+    alpha, total = n_q // dnum, n_q + n_p
+    x = ntt_inverse_batch(c, tabs[:n_q])
+    up = np.zeros((dnum, total, N), dtype=np.uint64)
+    for d in range(dnum):
+        dig = list(range(d * alpha, (d + 1) * alpha))
+        tgt = [g for g in range(total) if g not in dig]
+        conv = bconv_hps(x[dig], [moduli[g] for g in dig], [moduli[g] for g in tgt])
+        up[d, tgt] = ntt_forward_batch(conv, [tabs[g] for g in tgt])
+        up[d, dig] = c[dig]
+    return up
+
+
+def keyswitch_moddown(acc, moduli, n_q, n_p, tabs):
+    """acc [n_q+n_p][N] NTT domain -> [n_q][N]: (acc - BaseConv_{P->Q}(acc mod P)) * P^-1 mod q_l."""
+    acc = np.ascontiguousarray(acc, dtype=np.uint64)
+    t = ntt_inverse_batch(acc[n_q:], tabs[n_q:])
+    conv = ntt_forward_batch(bconv_hps(t, moduli[n_q:], moduli[:n_q]), tabs[:n_q])
+    out = np.zeros((n_q, acc.shape[1]), dtype=np.uint64)
+    P = 1
+    for p in moduli[n_q:]:
+        P *= int(p)
+    for l in range(n_q):
+        q = int(moduli[l])
+        pinv = pow(P % q, -1, q)
+        d = (acc[l].astype(object) - conv[l].astype(object)) % q
+        out[l] = np.array((d * pinv) % q, dtype=np.uint64)
+    return out
+
+
+def keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs):
+    """c [n_q][N]; evk [dnum][2][n_q+n_p][N]; returns [2][n_q][N] (all NTT domain)."""
+    up = keyswitch_modup(c, moduli, n_q, n_p, dnum, tabs)
+    acc = pmult_accum(np.ascontiguousarray(evk, dtype=np.uint64), up, moduli)       # terms = digits, "plaintext" = up_d
+    return np.stack([keyswitch_moddown(acc[p], moduli, n_q, n_p, tabs) for p in range(2)])
