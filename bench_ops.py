@@ -86,7 +86,9 @@ def main():
     print(json.dumps({"metric": "ModUp base-conversion digits/s", "value": 1e3 / (ms_s + ms_c), "unit": "digits/s",
                       "ms_scale": ms_s, "ms_contract": ms_c, "dtype": "u64",
                       "config": {"workload": "C5 kernels: one digit, N=2^17, alpha=16 -> 48 target limbs (HPS)"},
-                      "roofline": {"bound": "integer multiplier pipe (dense contraction)", "mulmods_per_s": mm / ((ms_s + ms_c) * 1e-3),
+                      "roofline": {"bound": "tensor pipe (byte-split mma.sync u8, 8 cycles per m16n8k32 per sub-partition) + integer epilogue (one 128-bit Barrett per output)",
+                                   "imma_per_launch": (N // 16) * (K * 2) * ((alpha + 3) // 4), "tensor_pipe_frac": (N // 16) * (K * 2) * ((alpha + 3) // 4) * 8 / (592 * 1.965e9) / (ms_c * 1e-3),
+                                   "mulmods_per_s": mm / ((ms_s + ms_c) * 1e-3),
                                    "hbm_achieved_GBs": algo / ((ms_s + ms_c) * 1e-3) / 1e9, "hbm_peak_GBs": peak,
                                    "algorithmic_bytes_per_digit": algo}}))
 

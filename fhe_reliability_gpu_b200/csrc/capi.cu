@@ -616,6 +616,7 @@ extern "C" int b200fhe_bconv_destroy(b200fhe_bconv* p) {
     if (p->d_dst) cudaFree(p->d_dst);
     if (p->d_inv) cudaFree(p->d_inv);
     if (p->d_hat) cudaFree(p->d_hat);
+    if (p->d_btab) cudaFree(p->d_btab);
     if (p->d_y) cudaFree(p->d_y);
     if (p->d_io) cudaFree(p->d_io);
     delete p;
@@ -636,7 +637,7 @@ extern "C" int b200fhe_bconv_create(b200fhe_ctx* c, const int* src_idx, int m, c
         dst[k] = (u32)dst_idx[k];
     }
     std::vector<ulonglong2> inv(m);
-    std::vector<uint64_t> hat((size_t)K * m);
+    std::vector<uint64_t> hat((size_t)K * m), raw((size_t)K * m);
     for (int j = 0; j < m; j++) {
         const uint64_t pj = c->moduli[src[j]];
         uint64_t h = 1;
@@ -650,6 +651,7 @@ extern "C" int b200fhe_bconv_create(b200fhe_ctx* c, const int* src_idx, int m, c
             for (int i = 0; i < m; i++)
                 if (i != j) g = nt::mulmod(g, c->moduli[src[i]] % qk, qk);
             hat[(size_t)k * m + j] = (g & 0x3fffffffull) | ((g >> 30) << 32);
+            raw[(size_t)k * m + j] = g;
         }
     }
     CK(cudaSetDevice(c->device));
@@ -664,6 +666,29 @@ extern "C" int b200fhe_bconv_create(b200fhe_ctx* c, const int* src_idx, int m, c
     if (e == cudaSuccess) e = cudaMemcpy(p->d_dst, dst.data(), sizeof(u32) * K, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(p->d_inv, inv.data(), sizeof(ulonglong2) * m, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(p->d_hat, hat.data(), sizeof(uint64_t) * K * m, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && m <= 16 && !getenv("B200FHE_BCONV_NO_TC")) {
+        // B fragments of mma.m16n8k32 (col-major 32 x 8, lane = 4 g' + t holds k = 4t..4t+3 (+16) of column g'), laid out
+        // [n-tile u][k-step s][target][e = (g' & 1) * 4 + t]: column g' of n-tile u = digit 2u + (g' & 1) of target base + g'/2
+        const int KS = (m + 3) / 4;
+        std::vector<uint2> bt((size_t)8 * KS * K * 8);
+        for (int u = 0; u < 8; u++)
+            for (int s = 0; s < KS; s++)
+                for (int k = 0; k < K; k++)
+                    for (int el = 0; el < 8; el++) {
+                        const int digit = 2 * u + (el >> 2), t = el & 3;
+                        uint32_t w[2] = {0, 0};
+                        for (int half = 0; half < 2; half++)
+                            for (int cb = 0; cb < 4; cb++) {
+                                const int kidx = 32 * s + 16 * half + 4 * t + cb, j = kidx / 8, a = kidx % 8, sh = digit - a;
+                                uint32_t byte = 0;
+                                if (j < m && sh >= 0 && sh < 8) byte = (uint32_t)((raw[(size_t)k * m + j] >> (8 * sh)) & 0xff);
+                                w[half] |= byte << (8 * cb);
+                            }
+                        bt[(((size_t)u * KS + s) * K + k) * 8 + el] = make_uint2(w[0], w[1]);
+                    }
+        e = cudaMalloc(&p->d_btab, sizeof(uint2) * bt.size());
+        if (e == cudaSuccess) e = cudaMemcpy(p->d_btab, bt.data(), sizeof(uint2) * bt.size(), cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) {
         b200fhe_bconv_destroy(p);
         return b200_set_err(B200FHE_ECUDA, "bconv_create: %s", cudaGetErrorString(e));
@@ -684,7 +709,12 @@ extern "C" int b200fhe_bconv_scale(b200fhe_bconv* p, const uint64_t* d_x, uint64
 extern "C" int b200fhe_bconv_contract(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t k0, size_t kcount, void* stream) {
     if (!p || (kcount && (!d_y || !d_out)) || k0 + kcount > (size_t)p->K) return b200_set_err(B200FHE_EINVAL, "bconv_contract: bad arguments");
     CK(cudaSetDevice(p->ctx->device));
-    int rc = launch_bconv_contract((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, (const u64*)p->d_hat, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
+    int rc;
+    if (p->d_btab)
+        rc = launch_bconv_contract_tc((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, p->d_btab, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
+                                      (u32)k0, (u32)kcount, (cudaStream_t)stream);
+    else
+        rc = launch_bconv_contract((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, (const u64*)p->d_hat, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
                                    (u32)k0, (u32)kcount, (cudaStream_t)stream);
     if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_contract: source base too large for shared memory (m=%d)", p->m);
     if (kcount) g_launches++;

@@ -54,6 +54,9 @@ int launch_bconv_scale(const u64* x, u64* y, const B200Mod* mods, const u32* src
                        cudaStream_t s);
 int launch_bconv_contract(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const u64* hat, u32 N, u32 m, u32 K, u32 k0,
                           u32 kcount, cudaStream_t s);
+// tensor-core (byte-split, mma.sync u8) contraction for source bases of at most 16 moduli; btab [8][ceil(m/4)][K][8] fragments
+int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K,
+                             u32 k0, u32 kcount, cudaStream_t s);
 
 }  // namespace b200
 
@@ -94,6 +97,7 @@ struct b200fhe_bconv {
     u32* d_dst = nullptr;            // [K]
     ulonglong2* d_inv = nullptr;     // [m] (P/p_j)^-1 mod p_j with Shoup quotient
     u64* d_hat = nullptr;            // [K][m] (P/p_j) mod q_k, 30-bit halves packed
+    uint2* d_btab = nullptr;         // m <= 16: the same constants as byte-split tensor-core B fragments (bconv_kernels.cu)
     u64* d_y = nullptr;              // [m][N] scratch for the single-GPU path
     u64* d_io = nullptr;             // host-buffer path staging, grown on demand
     size_t io_words = 0;

@@ -161,9 +161,8 @@ __device__ __forceinline__ u64 canon2(u64 v, u64 q) {
 
 // full a*b mod q, a,b < 2^64 with a*b < q*2^64 is NOT required: generic 128-bit
 // Barrett with the two-word ratio (SEAL barrett_reduce_128).  Result in [0,q).
-__device__ __forceinline__ u64 barrett128(u64 lo, u64 hi, const B200Mod& m) {
+__device__ __forceinline__ u64 barrett128_raw(u64 lo, u64 hi, u64 q, u64 r0, u64 r1) {
     // floor(x * ratio / 2^128), x = hi:lo
-    u64 r0 = m.ratio0, r1 = m.ratio1;
     u64 carry = __umul64hi(lo, r0);
     u64 t1lo = lo * r1, t1hi = __umul64hi(lo, r1);
     u64 s = t1lo + carry;
@@ -172,8 +171,11 @@ __device__ __forceinline__ u64 barrett128(u64 lo, u64 hi, const B200Mod& m) {
     u64 s2 = s + t2lo;
     u64 c2 = t2hi + (s2 < t2lo);
     u64 quo = hi * r1 + c1 + c2;
-    u64 r = lo - quo * m.q;
-    return r >= m.q ? r - m.q : r;
+    u64 r = lo - quo * q;
+    return r >= q ? r - q : r;
+}
+__device__ __forceinline__ u64 barrett128(u64 lo, u64 hi, const B200Mod& m) {
+    return barrett128_raw(lo, hi, m.q, m.ratio0, m.ratio1);
 }
 __device__ __forceinline__ u64 mulmod_barrett(u64 a, u64 b, const B200Mod& m) {
     return barrett128(a * b, __umul64hi(a, b), m);
