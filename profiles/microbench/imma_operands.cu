@@ -26,6 +26,8 @@ __global__ void __launch_bounds__(512, 1) k(int iters, int* out, unsigned long l
             for (int r = 0; r < 4; r++) a[m][s][r] = threadIdx.x * 0x01010101u + m * 77 + s * 13 + r;
 #pragma unroll
     for (int u = 0; u < 8; u++) { b[u][0] = threadIdx.x * 3 + u; b[u][1] = threadIdx.x * 5 + u; }
+    extern __shared__ uint2 sm[];
+    if (MODE == 4) for (int i = threadIdx.x; i < 32 * 12 * 32; i += blockDim.x) sm[i] = make_uint2(i, i * 7);
     __syncthreads();
     unsigned long long t0 = clock64();
     for (int it = 0; it < iters; it++) {
@@ -36,6 +38,10 @@ __global__ void __launch_bounds__(512, 1) k(int iters, int* out, unsigned long l
                 if (MODE == 0) { mma(acc[0][u], a[0][0], b[0][0], b[0][1]); mma(acc[1][u], a[0][0], b[0][0], b[0][1]); }   // same operands
                 if (MODE == 1) { mma(acc[0][u], a[0][s], b[u][0], b[u][1]); mma(acc[1][u], a[1][s], b[u][0], b[u][1]); }   // kernel pattern
                 if (MODE == 2) { mma(acc[0][u], a[0][s], b[u][0], b[u][1]); mma(acc[1][u], a[0][s], b[u][0], b[u][1]); }   // A fixed per k-step
+                if (MODE == 4) {   // kernel pattern with the B fragment loaded from shared memory right before its two IMMAs
+                    const uint2 bb = sm[((u * 4 + s) * 12 + (it & 7)) * 32 + (threadIdx.x & 31)];
+                    mma(acc[0][u], a[0][s], bb.x, bb.y); mma(acc[1][u], a[1][s], bb.x, bb.y);
+                }
                 if (MODE == 3) { mma(acc[0][u], a[0][s], b[0][0], b[0][1]); mma(acc[1][u], a[1][s], b[0][0], b[0][1]); }   // B fixed
             }
     }
@@ -54,8 +60,10 @@ void run(const char* name, int warps_per_smsp) {
     int* out; unsigned long long* cyc;
     const int threads = 128 * warps_per_smsp, blocks = 148, iters = 1024;
     cudaMalloc(&out, sizeof(int) * threads * blocks); cudaMalloc(&cyc, 8);
-    k<MODE><<<blocks, threads>>>(8, out, cyc);
-    k<MODE><<<blocks, threads>>>(iters, out, cyc);
+    const size_t smem = MODE == 4 ? 32 * 12 * 32 * sizeof(uint2) : 0;
+    cudaFuncSetAttribute(k<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k<MODE><<<blocks, threads, smem>>>(8, out, cyc);
+    k<MODE><<<blocks, threads, smem>>>(iters, out, cyc);
     cudaDeviceSynchronize();
     unsigned long long c; cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
     printf("%-34s warps/SMSP %d : %.2f cycles per IMMA per SMSP  %s\n", name, warps_per_smsp, (double)c / iters / 64 / warps_per_smsp,
@@ -69,6 +77,7 @@ int main() {
         run<1>("kernel pattern (A alt., B per pair)", w);
         run<2>("A per k-step, B per pair", w);
         run<3>("A alternating, B fixed", w);
+        run<4>("kernel pattern, B from shared", w);
     }
     return 0;
 }
