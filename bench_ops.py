@@ -81,10 +81,16 @@ def main():
     o = torch.zeros((K, N), dtype=torch.int64, device="cuda")
     ms_s = timed(torch, lambda: conv.scale(x.data_ptr(), y.data_ptr(), 0, alpha, stream=sp), args.steps)
     ms_c = timed(torch, lambda: conv.contract(y.data_ptr(), o.data_ptr(), 0, K, stream=sp), args.steps)
+    ver = torch.zeros(alpha + K, dtype=torch.int32, device="cuda")
+    ms_u = timed(torch, lambda: conv.modup(x.data_ptr(), o.data_ptr(), stream=sp), args.steps)
+    ms_p = timed(torch, lambda: conv.modup_protected(x.data_ptr(), o.data_ptr(), ver.data_ptr(), None, stream=sp), args.steps)
+    assert int(ver.abs().sum().item()) == 0, "protected conversion flagged a fault-free run"
     algo = (alpha + K) * N * 8
     mm = alpha * (1 + K) * N
     print(json.dumps({"metric": "ModUp base-conversion digits/s", "value": 1e3 / (ms_s + ms_c), "unit": "digits/s",
                       "ms_scale": ms_s, "ms_contract": ms_c, "dtype": "u64",
+                      "checksum_carrying": {"ms_unprotected": ms_u, "ms_protected": ms_p, "overhead_pct": 100.0 * (ms_p / ms_u - 1.0),
+                                            "checks": "scale, y in memory, contraction: per limb, sums accumulated inside the conversion kernels"},
                       "config": {"workload": "C5 kernels: one digit, N=2^17, alpha=16 -> 48 target limbs (HPS)"},
                       "roofline": {"bound": "tensor pipe (byte-split mma.sync u8, 8 cycles per m16n8k32 per sub-partition) + integer epilogue (one 128-bit Barrett per output)",
                                    "imma_per_launch": (N // 16) * (K * 2) * ((alpha + 3) // 4), "tensor_pipe_frac": (N // 16) * (K * 2) * ((alpha + 3) // 4) * 8 / (592 * 1.965e9) / (ms_c * 1e-3),

@@ -47,6 +47,8 @@ SIGNATURES = {
     "b200fhe_bconv_contract": (i32, [vp, vp, vp, sz, sz, vp]),
     "b200fhe_bconv_modup": (i32, [vp, vp, vp, vp]),
     "b200fhe_bconv_modup_host": (i32, [vp, U64P, U64P]),
+    "b200fhe_bconv_modup_protected": (i32, [vp, vp, vp, vp, vp, vp, sz, vp]),
+    "b200fhe_bconv_modup_protected_host": (i32, [vp, U64P, U64P, C.POINTER(C.c_uint32), U64P, vp, sz]),
     "b200fhe_keyswitch_create": (i32, [vp, i32, i32, i32, C.POINTER(vp)]),
     "b200fhe_keyswitch_destroy": (i32, [vp]),
     "b200fhe_keyswitch_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(sz)]),
@@ -267,6 +269,35 @@ class BaseConv:
         out = np.zeros((self.K, self.N), dtype=np.uint64)
         check(lib().b200fhe_bconv_modup_host(self._h, _p(x), _p(out)))
         return out
+
+
+class BconvInject(C.Structure):
+    """b200fhe_bconv_inject: stage 1 = scale product, 2 = contraction output, 3 = y in memory between the kernels."""
+    _fields_ = [("stage", C.c_uint32), ("limb", C.c_uint32), ("coeff", C.c_uint64), ("xor_mask", C.c_uint64)]
+
+
+def _modup_protected_host(self, x, inject=()):
+    """Checksum-carrying ModUp (baseConv.py:42-98 bConv_ecc on the device): x [m][N] -> (out [K][N], verdict [m+K],
+    sums [m+K][2]).  inject: (stage, limb, coeff, xor_mask) tuples."""
+    x = np.ascontiguousarray(x, dtype=np.uint64)
+    assert x.shape == (self.m, self.N)
+    out = np.zeros((self.K, self.N), dtype=np.uint64)
+    verdict = np.zeros(self.m + self.K, dtype=np.uint32)
+    sums = np.zeros((self.m + self.K, 2), dtype=np.uint64)
+    arr = (BconvInject * max(len(inject), 1))()
+    for i, e in enumerate(inject):
+        arr[i] = BconvInject(*[int(v) for v in e])
+    check(lib().b200fhe_bconv_modup_protected_host(self._h, _p(x), _p(out), verdict.ctypes.data_as(C.POINTER(C.c_uint32)), _p(sums),
+                                                   C.cast(arr, vp), len(inject)))
+    return out, verdict, sums
+
+
+def _modup_protected(self, in_ptr, out_ptr, verdict_ptr, sums_ptr=None, stream=0):
+    check(lib().b200fhe_bconv_modup_protected(self._h, in_ptr, out_ptr, verdict_ptr, sums_ptr, None, 0, stream))
+
+
+BaseConv.modup_protected_host = _modup_protected_host
+BaseConv.modup_protected = _modup_protected
 
 
 class KeySwitch:

@@ -31,6 +31,80 @@ __global__ void __launch_bounds__(256) k_bconv_scale(const u64* __restrict__ x, 
     reinterpret_cast<ulonglong2*>(y)[off] = r;
 }
 
+// ---- checksum-carrying conversion (spec rfhe_framewk/src/baseConv.py:42-98 bConv_ecc) ----------------
+// The prototype appends e_j = sum_i x_j[i] mod p_j to every source limb, converts it with the data and compares, per
+// term, the converted checksum with the sum of the converted data.  Here the same linearity is checked per KERNEL with
+// sums accumulated where the data already is in registers (no extra pass over memory):
+//   scale:     sum_i y_j[i] == inv_j * sum_i x_j[i]  (mod p_j)                      per source limb j
+//   contract:  sum_i out_k[i] == sum_j hat_jk * (sum_i y_j[i])  (mod q_k)           per target limb k
+//   in between: the y sums at the producer's store equal the y sums at the consumer's load (memory / transfer fault)
+// Sums are exact integers kept as separate sums of the low and high 32-bit halves (each < 2^32 N); reduction mod the
+// moduli happens once, in k_bconv_prot_finalize.
+struct BconvInj {          // device copy of b200fhe_bconv_inject
+    u32 stage, limb;
+    u64 coeff, mask;
+};
+constexpr int kBconvMaxInj = 8;
+struct BconvInjList {
+    BconvInj e[kBconvMaxInj];
+    u32 n;
+};
+
+__device__ __forceinline__ u64 warp_sum64(u64 v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ void red_add64(u64* p, u64 v) { asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+
+// counters c1 [m][4] = {sum x lo32, sum x hi32, sum y lo32, sum y hi32}
+__global__ void __launch_bounds__(256) k_bconv_scale_prot(const u64* __restrict__ x, u64* __restrict__ y, const B200Mod* mods,
+                                                          const u32* src_idx, const ulonglong2* inv, u32 N, u32 j0, u64* c1,
+                                                          const __grid_constant__ BconvInjList inj) {
+    const u32 j = j0 + blockIdx.y;
+    const B200Mod m = mods[src_idx[j]];
+    const ulonglong2 w = inv[j];
+    const u64 nq = 0 - m.q;
+    u64 sxl = 0, sxh = 0, syl = 0, syh = 0;
+    constexpr int kPer = 4;                                   // coefficient pairs per thread: amortises the reductions
+    ulonglong2 v[kPer];
+    size_t idx[kPer];
+#pragma unroll
+    for (int r = 0; r < kPer; r++) {
+        idx[r] = ((size_t)blockIdx.x * kPer + r) * blockDim.x + threadIdx.x;
+        v[r] = idx[r] * 2 < N ? reinterpret_cast<const ulonglong2*>(x)[((size_t)blockIdx.y * N) / 2 + idx[r]] : make_ulonglong2(0, 0);
+    }
+#pragma unroll
+    for (int r = 0; r < kPer; r++) {
+        if (idx[r] * 2 >= N) continue;
+        ulonglong2 o;
+        o.x = canon2(shoup_mul(v[r].x, w.x, w.y, nq), m.q);
+        o.y = canon2(shoup_mul(v[r].y, w.x, w.y, nq), m.q);
+        for (u32 e = 0; e < inj.n; e++)                       // a faulty multiplier: the corrupted product is what gets stored AND summed
+            if (inj.e[e].stage == 1 && inj.e[e].limb == j) {
+                if (inj.e[e].coeff == idx[r] * 2) o.x ^= inj.e[e].mask;
+                if (inj.e[e].coeff == idx[r] * 2 + 1) o.y ^= inj.e[e].mask;
+            }
+        reinterpret_cast<ulonglong2*>(y)[((size_t)blockIdx.y * N) / 2 + idx[r]] = o;
+        sxl += (v[r].x & 0xffffffffull) + (v[r].y & 0xffffffffull); sxh += (v[r].x >> 32) + (v[r].y >> 32);
+        syl += (o.x & 0xffffffffull) + (o.y & 0xffffffffull); syh += (o.x >> 32) + (o.y >> 32);
+    }
+    // one reduction per CTA and counter (per-warp reductions to the same four addresses serialise in L2: 71 us instead of 8)
+    __shared__ u64 part[8][4];
+    sxl = warp_sum64(sxl); sxh = warp_sum64(sxh); syl = warp_sum64(syl); syh = warp_sum64(syh);
+    if ((threadIdx.x & 31) == 0) {
+        u64* pw = part[threadIdx.x >> 5];
+        pw[0] = sxl; pw[1] = sxh; pw[2] = syl; pw[3] = syh;
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        u64 v = 0;
+#pragma unroll
+        for (int w8 = 0; w8 < 8; w8++) v += part[w8][threadIdx.x];
+        red_add64(c1 + (size_t)j * 4 + threadIdx.x, v);
+    }
+}
+
 constexpr int kBcT = 4;          // outputs per accumulation tile
 constexpr int kBcChunk = 16;     // terms per carry-free accumulation chunk ((2^30)^2 * 16 = 2^64)
 
@@ -147,10 +221,14 @@ __device__ __forceinline__ void digits_value(const u32 (&S)[16], u64& lo, u64& h
     hi = (W[1] >> 32) + W[2] + (W[3] << 32) + (lo < W[0]);
 }
 
-template <int KS>
+// PROT: also accumulates the checksum sums: cin [m][2] = sums of the low / high halves of the y words as loaded (grid.y
+// slice 0 only), cout [K][2] = sums of the low / high halves of the outputs as stored (per-CTA shared-memory
+// accumulators, one global reduction per CTA and target).
+template <int KS, bool PROT>
 __global__ void __launch_bounds__(kTcWarps * 32, 2)
     k_bconv_contract_tc(const u64* __restrict__ y, u64* __restrict__ out, const B200Mod* mods, const u32* dst_idx,
-                        const uint2* __restrict__ btab /*[8][KS][K][8]*/, u32 N, u32 m, u32 K, u32 k0, u32 kcount, u32 per_cta) {
+                        const uint2* __restrict__ btab /*[8][KS][K][8]*/, u32 N, u32 m, u32 K, u32 k0, u32 kcount, u32 per_cta,
+                        u64* cin, u64* cout, const __grid_constant__ BconvInjList inj) {
     extern __shared__ __align__(16) uint2 sb[];                 // [8][KS][kc][8] fragments, then [kc] (q, ratio0, ratio1, -)
     const u32 ka = k0 + blockIdx.y * per_cta;                   // first target of this CTA
     const u32 kend = (k0 + kcount < ka + per_cta) ? k0 + kcount : ka + per_cta;
@@ -166,10 +244,15 @@ __global__ void __launch_bounds__(kTcWarps * 32, 2)
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
     ulonglong4* sq = reinterpret_cast<ulonglong4*>(sb + (size_t)8 * KS * kc * 8);
+    // PROT: per-warp checksum accumulators (plain read-add-write by one lane per entry: 64-bit shared atomics are CAS loops)
+    u64* so = reinterpret_cast<u64*>(sq + kc);                   // [kTcWarps][kc][2] output sums
+    u64* si = so + (size_t)kTcWarps * kc * 2;                    // [kTcWarps][16][2] input sums
     for (u32 k = threadIdx.x; k < kc; k += blockDim.x) {
         const B200Mod& mk = mods[dst_idx[ka + k]];
         sq[k] = make_ulonglong4(mk.q, mk.ratio0, mk.ratio1, 0);
     }
+    if (PROT)
+        for (u32 k = threadIdx.x; k < kTcWarps * (kc * 2 + 32); k += blockDim.x) so[k] = 0;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
@@ -189,6 +272,21 @@ __global__ void __launch_bounds__(kTcWarps * 32, 2)
                 a[mt][s][2] = (j1 < m && r0 < N) ? __ldg(y32 + ((size_t)j1 * N + r0) * 2 + (t & 1)) : 0;
                 a[mt][s][3] = (j1 < m && r1 < N) ? __ldg(y32 + ((size_t)j1 * N + r1) * 2 + (t & 1)) : 0;
             }
+        }
+        if (PROT && blockIdx.y == 0) {
+            // every (source limb, row, half) is held by exactly one fragment register of the warp: a[.][s][r] is the
+            // (t & 1) half of y[4s + (t >> 1) + 2 (r >> 1)][row]; rows >= N and limbs >= m were loaded as 0
+#pragma unroll
+            for (int s2 = 0; s2 < KS; s2++)
+#pragma unroll
+                for (int jr = 0; jr < 2; jr++) {
+                    u64 v = (u64)a[0][s2][2 * jr] + a[0][s2][2 * jr + 1] + a[1][s2][2 * jr] + a[1][s2][2 * jr + 1];
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    const u32 jj = 4 * s2 + (t >> 1) + 2 * jr;
+                    if (g == 0) si[(warp * 16 + jj) * 2 + (t & 1)] += v;
+                }
         }
         for (u32 kb = 0; kb < kc; kb += 4) {
             int acc[2][8][4];
@@ -240,6 +338,32 @@ __global__ void __launch_bounds__(kTcWarps * 32, 2)
 #endif
                 }
             }
+            if (PROT) {
+                for (u32 e = 0; e < inj.n; e++)                   // a faulty reduction: the corrupted output is stored AND summed
+                    if (inj.e[e].stage == 2 && live && inj.e[e].limb == ka + tk) {
+#pragma unroll
+                        for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                            for (int h = 0; h < 2; h++)
+                                if (inj.e[e].coeff == i0 + 16 * mt + 8 * h + g) res[mt][h] ^= inj.e[e].mask;
+                    }
+                u64 sl = 0, sh = 0;
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                    for (int h = 0; h < 2; h++)
+                        if (live && i0 + 16 * mt + 8 * h + g < N) { sl += res[mt][h] & 0xffffffffull; sh += res[mt][h] >> 32; }
+                // sum over the 8 lanes that own the same target (same t).  (REDUX with the four per-t lane masks was measured
+                // slower than these shuffles: 85 vs 75 us per launch.)
+                sl += __shfl_xor_sync(0xffffffffu, sl, 4); sh += __shfl_xor_sync(0xffffffffu, sh, 4);
+                sl += __shfl_xor_sync(0xffffffffu, sl, 8); sh += __shfl_xor_sync(0xffffffffu, sh, 8);
+                sl += __shfl_xor_sync(0xffffffffu, sl, 16); sh += __shfl_xor_sync(0xffffffffu, sh, 16);
+                if (g == 0 && live) {
+                    u64* pw = so + ((size_t)warp * kc + tk) * 2;
+                    pw[0] += sl;
+                    pw[1] += sh;
+                }
+            }
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {
 #pragma unroll
@@ -250,13 +374,31 @@ __global__ void __launch_bounds__(kTcWarps * 32, 2)
             }
         }
     }
+    if (PROT) {
+        __syncthreads();
+        for (u32 k = threadIdx.x; k < 2 * kc + 32; k += blockDim.x) {
+            u64 v = 0;
+            if (k < 2 * kc) {
+#pragma unroll
+                for (int w8 = 0; w8 < kTcWarps; w8++) v += so[(size_t)w8 * kc * 2 + k];
+                red_add64(cout + (size_t)ka * 2 + k, v);
+            } else if (blockIdx.y == 0) {
+                const u32 e = k - 2 * kc;
+#pragma unroll
+                for (int w8 = 0; w8 < kTcWarps; w8++) v += si[w8 * 32 + e];
+                if (e / 2 < m) red_add64(cin + e, v);
+            }
+        }
+    }
 }
 
-template <int KS>
+template <int KS, bool PROT>
 static void launch_tc(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K, u32 k0,
-                      u32 kcount, cudaStream_t s) {
-    const size_t per_target = (size_t)KS * 8 * 8 * sizeof(uint2) + sizeof(ulonglong4);   // fragment + constant bytes per target
-    const size_t budget = 100 * 1024;                                      // two CTAs per SM
+                      u32 kcount, cudaStream_t s, u64* cin, u64* cout, const BconvInjList& inj) {
+    // fragment + constant (+ checksum accumulator) bytes per target
+    const size_t per_target = (size_t)KS * 8 * 8 * sizeof(uint2) + sizeof(ulonglong4) + (PROT ? kTcWarps * 2 * sizeof(u64) : 0);
+    const size_t fixed = PROT ? kTcWarps * 32 * sizeof(u64) : 0;
+    const size_t budget = 108 * 1024;                                      // two CTAs per SM
     u32 ny = (u32)((kcount * per_target + budget - 1) / budget);
     u32 per_cta = ((kcount + ny - 1) / ny + 3) & ~3u;
     ny = (kcount + per_cta - 1) / per_cta;
@@ -266,22 +408,102 @@ static void launch_tc(const u64* y, u64* out, const B200Mod* mods, const u32* ds
     if (gx > blocks) gx = blocks;
     const u32 rounds = (blocks + gx - 1) / gx;
     gx = (blocks + rounds - 1) / rounds;
-    const size_t smem = per_target * (per_cta < kcount ? per_cta : kcount);
-    cudaFuncSetAttribute(k_bconv_contract_tc<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget + 4096);
-    k_bconv_contract_tc<KS><<<dim3(gx, ny), kTcWarps * 32, smem, s>>>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, per_cta);
+    const size_t smem = per_target * (per_cta < kcount ? per_cta : kcount) + fixed;
+    cudaFuncSetAttribute(k_bconv_contract_tc<KS, PROT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget + 4096);
+    k_bconv_contract_tc<KS, PROT><<<dim3(gx, ny), kTcWarps * 32, smem, s>>>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, per_cta,
+                                                                              cin, cout, inj);
+}
+
+template <bool PROT>
+static int launch_tc_ks(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K, u32 k0,
+                        u32 kcount, cudaStream_t s, u64* cin, u64* cout, const BconvInjList& inj) {
+    if (!kcount) return 0;
+    switch ((m + 3) / 4) {
+        case 1: launch_tc<1, PROT>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s, cin, cout, inj); break;
+        case 2: launch_tc<2, PROT>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s, cin, cout, inj); break;
+        case 3: launch_tc<3, PROT>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s, cin, cout, inj); break;
+        case 4: launch_tc<4, PROT>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s, cin, cout, inj); break;
+        default: return -1;
+    }
+    return 0;
 }
 
 // btab != nullptr and m <= 16: tensor-core path
 int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K,
                              u32 k0, u32 kcount, cudaStream_t s) {
-    if (!kcount) return 0;
-    switch ((m + 3) / 4) {
-        case 1: launch_tc<1>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s); break;
-        case 2: launch_tc<2>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s); break;
-        case 3: launch_tc<3>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s); break;
-        case 4: launch_tc<4>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s); break;
-        default: return -1;
+    BconvInjList none;
+    none.n = 0;
+    return launch_tc_ks<false>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, s, nullptr, nullptr, none);
+}
+
+// One warp per checked limb.  counters: c1 [m][4] | cin [m][2] | cout [K][2]; two sets alternate between calls.
+// verdict [m + K]: source limb j: bit 0 = scale check failed, bit 1 = y changed between the two kernels;
+//                  target limb k (at m + k): bit 0 = contraction check failed.  sums (optional) [m + K][2] = (lhs, rhs).
+__global__ void k_bconv_prot_finalize(u64* counters, u64* next_counters, const B200Mod* mods, const u32* src_idx, const u32* dst_idx, const ulonglong2* inv,
+                                      const u64* hat /*[K][m] packed 30-bit halves*/, u32 m, u32 K, u32* verdict, u64* sums) {
+    const u32 i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;     // one warp per check
+    // the NEXT call's counter set is cleared here (the two sets alternate), which saves a clearing launch per call
+    for (u32 z = blockIdx.x * blockDim.x + threadIdx.x; z < 6 * m + 2 * K; z += gridDim.x * blockDim.x) next_counters[z] = 0;
+    if (i >= m + K) return;
+    u64* c1 = counters;
+    u64* cin = counters + (size_t)4 * m;
+    u64* cout = cin + (size_t)2 * m;
+    // (lo32 sum) + (hi32 sum) 2^32 as a 128-bit integer, reduced mod q
+    auto value_mod = [](u64 sl, u64 sh, const B200Mod& mq) {
+        const u64 lo = sl + (sh << 32);
+        const u64 hi = (sh >> 32) + (lo < sl);
+        return barrett128(lo, hi, mq);
+    };
+    u64 lhs, rhs;
+    u32 v = 0;
+    if (i < m) {
+        const B200Mod mq = mods[src_idx[i]];
+        lhs = value_mod(c1[4 * i + 2], c1[4 * i + 3], mq);                                    // sum y
+        rhs = mulmod_barrett(value_mod(c1[4 * i + 0], c1[4 * i + 1], mq), inv[i].x, mq);      // inv * sum x
+        if (lhs != rhs) v |= 1u;
+        if (c1[4 * i + 2] != cin[2 * i] || c1[4 * i + 3] != cin[2 * i + 1]) v |= 2u;
+    } else {
+        const u32 k = i - m;
+        const B200Mod mq = mods[dst_idx[k]];
+        lhs = value_mod(cout[2 * k], cout[2 * k + 1], mq);                                    // sum out
+        u64 term = 0;                                                                         // lane j: hat_jk * (sum y_j mod q_k)
+        if (lane < m) {
+            const u64 hp = hat[(size_t)k * m + lane];
+            const u64 hv = (hp & 0x3fffffffull) + ((hp >> 32) << 30);
+            term = mulmod_barrett(value_mod(cin[2 * lane], cin[2 * lane + 1], mq), hv, mq);
+        }
+        term = warp_sum64(term);                                                              // m <= 16 terms < 2^60 each
+        rhs = barrett128(term, 0, mq);
+        if (lhs != rhs) v |= 1u;
     }
+    if (lane == 0) {
+        verdict[i] = v;
+        if (sums) { sums[2 * i] = lhs; sums[2 * i + 1] = rhs; }
+    }
+}
+__global__ void k_bconv_xor(u64* y, size_t idx, u64 mask) { y[idx] ^= mask; }
+
+// Protected ModUp of one digit on one GPU: scale -> [memory-fault injection] -> contraction -> finalize.
+// inj: host array of n_inj entries {stage, limb, coeff, mask}; stage 1 = scale product, 2 = contraction output, 3 = y in memory.
+int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
+                                 const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
+                                 u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches) {
+    if (!btab || m > 16 || n_inj > (u32)kBconvMaxInj) return -1;
+    BconvInjList il;
+    il.n = n_inj;
+    for (u32 e = 0; e < n_inj; e++) il.e[e] = reinterpret_cast<const BconvInj*>(inj_host)[e];
+    dim3 grid((N / 2 + 1023) / 1024, m);
+    k_bconv_scale_prot<<<grid, 256, 0, s>>>(x, y, mods, src_idx, inv, N, 0, counters, il);
+    unsigned long long nl = 1;
+    for (u32 e = 0; e < n_inj; e++)
+        if (il.e[e].stage == 3 && il.e[e].limb < m && il.e[e].coeff < N) {
+            k_bconv_xor<<<1, 1, 0, s>>>(y, (size_t)il.e[e].limb * N + il.e[e].coeff, il.e[e].mask);
+            nl++;
+        }
+    int rc = launch_tc_ks<true>(y, out, mods, dst_idx, btab, N, m, K, 0, K, s, counters + (size_t)4 * m, counters + (size_t)6 * m, il);
+    if (rc) return rc;
+    k_bconv_prot_finalize<<<(m + K + 3) / 4, 128, 0, s>>>(counters, next_counters, mods, src_idx, dst_idx, inv, hat, m, K, verdict, sums);
+    if (launches) *launches += nl + 2;
     return 0;
 }
 

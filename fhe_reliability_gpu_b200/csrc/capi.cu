@@ -617,6 +617,7 @@ extern "C" int b200fhe_bconv_destroy(b200fhe_bconv* p) {
     if (p->d_inv) cudaFree(p->d_inv);
     if (p->d_hat) cudaFree(p->d_hat);
     if (p->d_btab) cudaFree(p->d_btab);
+    if (p->d_cnt) cudaFree(p->d_cnt);
     if (p->d_y) cudaFree(p->d_y);
     if (p->d_io) cudaFree(p->d_io);
     delete p;
@@ -745,6 +746,56 @@ extern "C" int b200fhe_bconv_modup_host(b200fhe_bconv* p, const uint64_t* h_in, 
     int rc = b200fhe_bconv_modup(p, (const uint64_t*)p->d_io, (uint64_t*)(p->d_io + wi), s);
     if (rc) return rc;
     CK(cudaMemcpyAsync(h_out, p->d_io + wi, sizeof(uint64_t) * wo, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+extern "C" int b200fhe_bconv_modup_protected(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_out, uint32_t* d_verdict, uint64_t* d_sums,
+                                             const b200fhe_bconv_inject* inject, size_t n_inject, void* stream) {
+    if (!p || !d_in || !d_out || !d_verdict) return b200_set_err(B200FHE_EINVAL, "bconv_modup_protected: null argument");
+    if (n_inject > B200FHE_BCONV_MAX_INJECT || (n_inject && !inject)) return b200_set_err(B200FHE_EINVAL, "bconv_modup_protected: bad injection plan");
+    if (!p->d_btab) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup_protected: needs the tensor-core plan (at most 16 source moduli)");
+    CK(cudaSetDevice(p->ctx->device));
+    const size_t n_cnt = 6 * (size_t)p->m + 2 * (size_t)p->K;
+    if (!p->d_cnt) {
+        CK(cudaMalloc(&p->d_cnt, sizeof(uint64_t) * 2 * n_cnt));
+        CK(cudaMemsetAsync(p->d_cnt, 0, sizeof(uint64_t) * 2 * n_cnt, (cudaStream_t)stream));
+        p->cnt_set = 0;
+    }
+    u64* cur = p->d_cnt + (size_t)p->cnt_set * n_cnt;
+    u64* nxt = p->d_cnt + (size_t)(p->cnt_set ^ 1) * n_cnt;
+    p->cnt_set ^= 1;
+    static_assert(sizeof(b200fhe_bconv_inject) == 24, "layout shared with BconvInj");
+    int rc = launch_bconv_modup_protected((const u64*)d_in, p->d_y, (u64*)d_out, p->ctx->d_mods, p->d_src, p->d_dst, p->d_inv, p->d_hat, p->d_btab,
+                                          (u32)p->ctx->N, (u32)p->m, (u32)p->K, cur, nxt, d_verdict, (u64*)d_sums, inject, (u32)n_inject,
+                                          (cudaStream_t)stream, &g_launches);
+    if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup_protected: unsupported plan");
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200fhe_bconv_modup_protected_host(b200fhe_bconv* p, const uint64_t* h_in, uint64_t* h_out, uint32_t* h_verdict,
+                                                  uint64_t* h_sums, const b200fhe_bconv_inject* inject, size_t n_inject) {
+    if (!p || !h_in || !h_out || !h_verdict) return b200_set_err(B200FHE_EINVAL, "bconv_modup_protected_host: null argument");
+    b200fhe_ctx* c = p->ctx;
+    CK(cudaSetDevice(c->device));
+    const size_t wi = (size_t)p->m * c->N, wo = (size_t)p->K * c->N, nchk = (size_t)p->m + p->K;
+    const size_t need = wi + wo + 2 * nchk + (nchk + 1) / 2;          // data | sums | verdict (u32)
+    if (p->io_words < need) {
+        if (p->d_io) cudaFree(p->d_io);
+        p->d_io = nullptr; p->io_words = 0;
+        CK(cudaMalloc(&p->d_io, sizeof(uint64_t) * need));
+        p->io_words = need;
+    }
+    cudaStream_t s = c->own_stream;
+    u64* d_sums = p->d_io + wi + wo;
+    uint32_t* d_ver = reinterpret_cast<uint32_t*>(d_sums + 2 * nchk);
+    CK(cudaMemcpyAsync(p->d_io, h_in, sizeof(uint64_t) * wi, cudaMemcpyHostToDevice, s));
+    int rc = b200fhe_bconv_modup_protected(p, (const uint64_t*)p->d_io, (uint64_t*)(p->d_io + wi), d_ver, (uint64_t*)d_sums, inject, n_inject, s);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_out, p->d_io + wi, sizeof(uint64_t) * wo, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h_verdict, d_ver, sizeof(uint32_t) * nchk, cudaMemcpyDeviceToHost, s));
+    if (h_sums) CK(cudaMemcpyAsync(h_sums, d_sums, sizeof(uint64_t) * 2 * nchk, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     return 0;
 }

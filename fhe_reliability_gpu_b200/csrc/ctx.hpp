@@ -57,6 +57,10 @@ int launch_bconv_contract(const u64* y, u64* out, const B200Mod* mods, const u32
 // tensor-core (byte-split, mma.sync u8) contraction for source bases of at most 16 moduli; btab [8][ceil(m/4)][K][8] fragments
 int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K,
                              u32 k0, u32 kcount, cudaStream_t s);
+// checksum-carrying ModUp of one digit (scale + tensor-core contraction + finalize); counters: 6 m + 2 K words of scratch
+int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
+                                 const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
+                                 u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches);
 
 }  // namespace b200
 
@@ -99,6 +103,8 @@ struct b200fhe_bconv {
     u64* d_hat = nullptr;            // [K][m] (P/p_j) mod q_k, 30-bit halves packed
     uint2* d_btab = nullptr;         // m <= 16: the same constants as byte-split tensor-core B fragments (bconv_kernels.cu)
     u64* d_y = nullptr;              // [m][N] scratch for the single-GPU path
+    u64* d_cnt = nullptr;            // checksum counters of the protected path: two sets of 6 m + 2 K words, used alternately
+    int cnt_set = 0;
     u64* d_io = nullptr;             // host-buffer path staging, grown on demand
     size_t io_words = 0;
 };

@@ -169,6 +169,29 @@ def ecc_check(a, psi, mod, plan=()):
     return int(sums[0, 0]), int(sums[0, 1]), not bool(verdict[0])
 
 
+def bConv_ecc(residues, p_moduli, q_moduli, inject=()):
+    """rfhe_framewk/src/baseConv.py:42-98: base conversion that carries a checksum and raises
+    ValueError("ECC mismatch ...") when it does not survive.  residues[j][i] mod p_moduli[j] -> result[i][k] mod
+    q_moduli[k] (the prototype's orientation).  Values are the HPS conversion's (SEAL / Phantom fast_convert_array:
+    x + e P for a small e); the prototype's own bConv differs from it by multiples of P.
+    Needs len(residues[0]) = 2^k and every modulus NTT-friendly for that length (the library's context rule)."""
+    n = len(residues[0])
+    mods = [int(v) for v in list(p_moduli) + list(q_moduli)]
+    key = ("bconv", n, tuple(mods))
+    c = _ctx_cache.get(key)
+    if c is None:
+        ctx = B.Context(_log2(n), mods)
+        c = _ctx_cache[key] = (ctx, B.BaseConv(ctx, list(range(len(p_moduli))), list(range(len(p_moduli), len(mods)))))
+    x = np.array([[int(v) % int(p) for v in row] for row, p in zip(residues, p_moduli)], dtype=np.uint64)
+    out, verdict, _ = c[1].modup_protected_host(x, inject=inject)
+    bad = np.nonzero(verdict)[0]
+    if len(bad):
+        i = int(bad[0])
+        where = "source modulus index %d" % i if i < len(p_moduli) else "target modulus index %d" % (i - len(p_moduli))
+        raise ValueError("ECC mismatch at %s" % where)
+    return [[int(out[k][i]) for k in range(len(q_moduli))] for i in range(n)]
+
+
 def four_step_with_protection_vector(a, N, mod=MOD, g=G, fault=None):
     """reliability_test/four_step_ntt_prot.py:196-252: returns (y, checks) with
     checks = {"stage1": {lhs, rhs, ok}, "stage2": {...}, "y_matches_reference": bool}, every number

@@ -213,6 +213,26 @@ int b200fhe_bconv_contract(b200fhe_bconv* plan, const uint64_t* d_y, uint64_t* d
 int b200fhe_bconv_modup(b200fhe_bconv* plan, const uint64_t* d_in, uint64_t* d_out, void* stream);
 int b200fhe_bconv_modup_host(b200fhe_bconv* plan, const uint64_t* h_in, uint64_t* h_out);
 
+/* ---- checksum-carrying base conversion ------------------------
+ * rfhe_framewk/src/baseConv.py:42-98 bConv_ecc carries e_j = sum_i x_j[i] mod p_j through the conversion and
+ * raises on a mismatch.  The device form checks the same linearity per kernel, with the sums accumulated inside the
+ * conversion kernels: scale (sum y_j == inv_j sum x_j mod p_j), contraction (sum out_k == sum_j hat_jk sum y_j mod
+ * q_k), and that y did not change between the two kernels.  Plans with at most 16 source moduli.
+ * d_verdict [m + K]: entry j < m: bit 0 = scale check failed, bit 1 = y changed in memory; entry m + k: bit 0 =
+ * contraction check failed.  d_sums (optional, may be NULL) [m + K][2] = (lhs, rhs) of each check. */
+typedef struct b200fhe_bconv_inject {
+    uint32_t stage;      /* 1: product of the scale kernel; 2: output of the contraction; 3: y in memory between them */
+    uint32_t limb;       /* source limb j (stage 1, 3) or target limb k (stage 2) */
+    uint64_t coeff;
+    uint64_t xor_mask;
+} b200fhe_bconv_inject;
+#define B200FHE_BCONV_MAX_INJECT 8
+int b200fhe_bconv_modup_protected(b200fhe_bconv* plan, const uint64_t* d_in, uint64_t* d_out, uint32_t* d_verdict, uint64_t* d_sums,
+                                  const b200fhe_bconv_inject* inject, size_t n_inject, void* stream);
+/* Host buffers; raises nothing itself: the caller maps a non-zero verdict to the prototype's ValueError("ECC mismatch"). */
+int b200fhe_bconv_modup_protected_host(b200fhe_bconv* plan, const uint64_t* h_in, uint64_t* h_out, uint32_t* h_verdict,
+                                       uint64_t* h_sums, const b200fhe_bconv_inject* inject, size_t n_inject);
+
 /* ---- hybrid key-switch: ModUp -> evk inner product -> ModDown -------------------
  * The work inside Phantom's relinearize_inplace / rotate_inplace (reliability_test/dotprod_test.cu:114,146)
  * and SEAL's switch_key_inplace (callgrind.out.ckks:11081; cost split profile_framewk/draw_dnum.py:5-9).

@@ -284,3 +284,50 @@ def keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs):
     up = keyswitch_modup(c, moduli, n_q, n_p, dnum, tabs)
     acc = pmult_accum(np.ascontiguousarray(evk, dtype=np.uint64), up, moduli)       # terms = digits, "plaintext" = up_d
     return np.stack([keyswitch_moddown(acc[p], moduli, n_q, n_p, tabs) for p in range(2)])
+
+
+# ---------------------------------------------------------------- checksum-carrying base conversion
+def bconv_hps_protected(x, p, qo, inject=()):
+    """HPS conversion with the linearity checks of rfhe_framewk/src/baseConv.py:42-98 (bConv_ecc) applied per step:
+    scale (sum y_j == inv_j sum x_j mod p_j), contraction (sum out_k == sum_j hat_jk sum y_j mod q_k), and y unchanged
+    between the two.  inject: (stage, limb, coeff, xor_mask); stage 1 = scale product, 2 = contraction output,
+    3 = y in memory between the steps.  Returns (out [K][N], verdict [m+K], sums [m+K][2]).  Python integers: small N."""
+    x = np.ascontiguousarray(x, dtype=np.uint64)
+    m, N = x.shape
+    K = len(qo)
+    p = [int(v) for v in p]; qo = [int(v) for v in qo]
+    P = 1
+    for v in p:
+        P *= v
+    xs = [[int(v) for v in row] for row in x]
+    inv = [pow((P // p[j]) % p[j], -1, p[j]) for j in range(m)]
+    y = [[(xs[j][i] * inv[j]) % p[j] for i in range(N)] for j in range(m)]
+    for st, limb, coeff, mask in inject:
+        if st == 1:
+            y[limb][coeff] ^= int(mask)
+    sum_x = [sum(row) for row in xs]
+    sum_y_prod = [sum(row) for row in y]
+    for st, limb, coeff, mask in inject:
+        if st == 3:
+            y[limb][coeff] ^= int(mask)
+    sum_y = [sum(row) for row in y]
+    hat = [[(P // p[j]) % qo[k] for j in range(m)] for k in range(K)]
+    out = np.zeros((K, N), dtype=np.uint64)
+    for k in range(K):
+        col = [sum(y[j][i] * hat[k][j] for j in range(m)) % qo[k] for i in range(N)]
+        for st, limb, coeff, mask in inject:
+            if st == 2 and limb == k:
+                col[coeff] ^= int(mask)
+        out[k] = np.array(col, dtype=np.uint64)
+    verdict = np.zeros(m + K, dtype=np.uint32)
+    sums = np.zeros((m + K, 2), dtype=np.uint64)
+    for j in range(m):
+        lhs, rhs = sum_y_prod[j] % p[j], (sum_x[j] % p[j]) * inv[j] % p[j]
+        verdict[j] = (1 if lhs != rhs else 0) | (2 if sum_y_prod[j] != sum_y[j] else 0)
+        sums[j] = (lhs, rhs)
+    for k in range(K):
+        lhs = sum(int(v) for v in out[k]) % qo[k]
+        rhs = sum((sum_y[j] % qo[k]) * hat[k][j] for j in range(m)) % qo[k]
+        verdict[m + k] = 1 if lhs != rhs else 0
+        sums[m + k] = (lhs, rhs)
+    return out, verdict, sums
