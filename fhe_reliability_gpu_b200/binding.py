@@ -55,6 +55,10 @@ SIGNATURES = {
     "b200fhe_keyswitch_modup": (i32, [vp, vp, vp, vp]),
     "b200fhe_keyswitch_moddown": (i32, [vp, vp, vp, vp, sz, vp]),
     "b200fhe_keyswitch_apply": (i32, [vp, vp, vp, vp, vp, vp]),
+    "b200fhe_ct_tensor": (i32, [vp, vp, vp, vp, sz, sz, vp]),
+    "b200fhe_poly_add": (i32, [vp, vp, vp, sz, sz, sz, vp]),
+    "b200fhe_poly_sub": (i32, [vp, vp, vp, sz, sz, sz, vp]),
+    "b200fhe_galois_ntt": (i32, [vp, vp, vp, C.c_uint32, sz, vp]),
     "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
     "b200fhe_host_alloc": (i32, [C.POINTER(vp), sz]),
     "b200fhe_host_free": (i32, [vp]),

@@ -85,13 +85,13 @@ extern "C" int b200fhe_keyswitch_destroy(b200fhe_keyswitch* k) {
 }
 
 extern "C" int b200fhe_keyswitch_create(b200fhe_ctx* c, int n_q, int n_p, int dnum, b200fhe_keyswitch** out) {
-    if (!c || !out || n_q < 1 || n_p < 1 || dnum < 1) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: bad arguments");
+    if (!c || !out || n_q < 1 || n_p < 1 || dnum < 0) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: bad arguments");
     if (n_q + n_p != c->L) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: context holds %d moduli, need n_q + n_p = %d", c->L, n_q + n_p);
-    if (n_q % dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: n_q=%d not divisible by dnum=%d", n_q, dnum);
+    if (dnum && n_q % dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: n_q=%d not divisible by dnum=%d", n_q, dnum);
     if (c->N < 2) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: N too small");
     for (int i = 0; i < c->L; i++)
         if (!c->moduli[i] || !c->has_inverse[i]) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: modulus %d has no inverse tables", i);
-    const int alpha = n_q / dnum, total = n_q + n_p;
+    const int alpha = dnum ? n_q / dnum : 0, total = n_q + n_p;      // dnum == 0: ModDown-only plan (rescale / mod-switch)
     if (alpha > 64 || n_p > 64) return b200_set_err(B200FHE_EUNSUPPORTED, "keyswitch_create: digit or special base larger than 64 limbs");
     b200fhe_keyswitch* k = new b200fhe_keyswitch();
     k->ctx = c; k->n_q = n_q; k->n_p = n_p; k->dnum = dnum; k->alpha = alpha;
@@ -125,11 +125,11 @@ extern "C" int b200fhe_keyswitch_create(b200fhe_ctx* c, int n_q, int n_p, int dn
     }
     const size_t N = c->N;
     size_t o = 0;
-    k->o_x = o;    o += (size_t)n_q * N;                 // INTT(c)
-    k->o_y = o;    o += (size_t)(n_q > 2 * n_p ? n_q : 2 * n_p) * N;   // scaled digits; reused for the scaled P part of ModDown
-    k->o_up = o;   o += (size_t)dnum * total * N;        // raised digits
-    k->o_accq = o; o += (size_t)2 * n_q * N;
-    k->o_accp = o; o += (size_t)2 * n_p * N;
+    k->o_x = o;    o += dnum ? (size_t)n_q * N : 0;                                  // INTT(c)
+    k->o_y = o;    o += (size_t)(dnum && n_q > 2 * n_p ? n_q : 2 * n_p) * N;         // scaled digits; reused for the scaled P part of ModDown
+    k->o_up = o;   o += (size_t)dnum * total * N;                                    // raised digits
+    k->o_accq = o; o += dnum ? (size_t)2 * n_q * N : 0;
+    k->o_accp = o; o += dnum ? (size_t)2 * n_p * N : 0;
     k->o_conv = o; o += (size_t)2 * n_q * N;
     k->ws_words = o;
     cudaError_t e = cudaSetDevice(c->device);
@@ -147,6 +147,7 @@ extern "C" int b200fhe_keyswitch_create(b200fhe_ctx* c, int n_q, int n_p, int dn
 // steps 1-2: every digit of c raised to the full basis, NTT domain.  d_up [dnum][n_q + n_p][N].
 extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, void* stream) {
     if (!k || !d_c || !d_up) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: null argument");
+    if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
     CK(cudaSetDevice(c->device));
     cudaStream_t s = (cudaStream_t)stream;
@@ -204,6 +205,7 @@ extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d
 extern "C" int b200fhe_keyswitch_apply(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
                                        uint64_t* d_out, void* stream) {
     if (!k || !d_c || !d_evk_q || !d_evk_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: null argument");
+    if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
     const size_t N = c->N, nq = (size_t)k->n_q, np = (size_t)k->n_p, total = nq + np;
     uint64_t* up = k->d_ws + k->o_up;

@@ -242,6 +242,9 @@ int b200fhe_bconv_modup_protected_host(b200fhe_bconv* plan, const uint64_t* h_in
  * synchronisation), so a switch can be captured in a CUDA graph. */
 typedef struct b200fhe_keyswitch b200fhe_keyswitch;
 int b200fhe_keyswitch_create(b200fhe_ctx* ctx, int n_q, int n_p, int dnum, b200fhe_keyswitch** out);
+/* dnum = 0 makes a ModDown-only plan (no ModUp tables or workspace): with n_p = 1 its b200fhe_keyswitch_moddown is
+ * rescale_to_next / the division step of mod_switch_to_next (dotprod_test.cu:115: drop the last prime q_last,
+ * out_l = (c_l - [c]_q_last) q_last^-1 mod q_l = floor(c / q_last), no rounding term). */
 int b200fhe_keyswitch_destroy(b200fhe_keyswitch* plan);
 int b200fhe_keyswitch_info(const b200fhe_keyswitch* plan, int* n_q, int* n_p, int* dnum, size_t* workspace_bytes);
 
@@ -262,6 +265,19 @@ int b200fhe_keyswitch_moddown(b200fhe_keyswitch* plan, const uint64_t* d_acc_q, 
  * of digit d: 1 modulo the digit's moduli, 0 modulo the other ciphertext moduli). */
 int b200fhe_keyswitch_apply(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
                             uint64_t* d_out, void* stream);
+
+/* ---- evaluator steps around the key-switch (NTT-form polynomials [n_poly][L][N]) --------------------
+ * The element-wise / permutation kernels phantom::multiply, add_inplace and rotate_inplace run around the
+ * key-switch in reliability_test/dotprod_test.cu:113-152. */
+/* multiply: d_a, d_b [2][L][N] -> d_out [3][L][N] = (a0 b0, a0 b1 + a1 b0, a1 b1) mod q_l.  Inputs taken mod q. */
+int b200fhe_ct_tensor(b200fhe_ctx* ctx, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, size_t L, size_t start_mod,
+                      void* stream);
+/* add_inplace / sub_inplace over n_poly polynomials; inputs in [0,q). */
+int b200fhe_poly_add(b200fhe_ctx* ctx, uint64_t* d_a, const uint64_t* d_b, size_t n_poly, size_t L, size_t start_mod, void* stream);
+int b200fhe_poly_sub(b200fhe_ctx* ctx, uint64_t* d_a, const uint64_t* d_b, size_t n_poly, size_t L, size_t start_mod, void* stream);
+/* The permutation step of rotate_inplace (SEAL apply_galois_ntt): x -> x^galois_elt on n_limbs NTT-form limbs
+ * (modulus-independent), galois_elt odd in [1, 2N); out of place. */
+int b200fhe_galois_ntt(b200fhe_ctx* ctx, const uint64_t* d_in, uint64_t* d_out, uint32_t galois_elt, size_t n_limbs, void* stream);
 
 /* Measurement hooks (bench.py): one pass of the two-kernel transform
  * (pass 1 = first kernel, 2 = second), and the number of kernels this library

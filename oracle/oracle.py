@@ -331,3 +331,28 @@ def bconv_hps_protected(x, p, qo, inject=()):
         verdict[m + k] = 1 if lhs != rhs else 0
         sums[m + k] = (lhs, rhs)
     return out, verdict, sums
+
+
+# ---------------------------------------------------------------- evaluator steps around the key-switch
+def galois_coeff(a, g, q):
+    """x -> x^g on a coefficient-domain polynomial mod (x^N + 1, q): coefficient i moves to i g mod 2N, negated when it
+    wraps past N (SEAL GaloisTool::apply_galois; the permutation under rotate_inplace, dotprod_test.cu:146)."""
+    a = [int(v) for v in a]
+    N = len(a)
+    out = [0] * N
+    for i, v in enumerate(a):
+        idx = (i * g) % (2 * N)
+        if idx >= N:
+            out[idx - N] = (-v) % q
+        else:
+            out[idx] = v % q
+    return np.array(out, dtype=np.uint64)
+
+
+def ct_tensor(a, b, moduli):
+    """a, b [2][L][N] NTT form -> [3][L][N] = (a0 b0, a0 b1 + a1 b0, a1 b1) (phantom::multiply, dotprod_test.cu:113)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64); b = np.ascontiguousarray(b, dtype=np.uint64)
+    d0 = pmult_accum(a[0][None, None], b[0][None], moduli)[0]
+    d2 = pmult_accum(a[1][None, None], b[1][None], moduli)[0]
+    d1 = pmult_accum(np.stack([a[0], a[1]])[:, None], np.stack([b[1], b[0]]), moduli)[0]
+    return np.stack([d0, d1, d2])
