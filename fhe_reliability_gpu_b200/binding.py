@@ -42,6 +42,7 @@ SIGNATURES = {
     "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_bconv_create": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, C.POINTER(vp)]),
+    "b200fhe_bconv_create_scaled": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, u64, C.POINTER(vp)]),
     "b200fhe_bconv_destroy": (i32, [vp]),
     "b200fhe_bconv_scale": (i32, [vp, vp, vp, sz, sz, vp]),
     "b200fhe_bconv_contract": (i32, [vp, vp, vp, sz, sz, vp]),
@@ -50,6 +51,7 @@ SIGNATURES = {
     "b200fhe_bconv_modup_protected": (i32, [vp, vp, vp, vp, vp, vp, sz, vp]),
     "b200fhe_bconv_modup_protected_host": (i32, [vp, U64P, U64P, C.POINTER(C.c_uint32), U64P, vp, sz]),
     "b200fhe_keyswitch_create": (i32, [vp, i32, i32, i32, C.POINTER(vp)]),
+    "b200fhe_keyswitch_create_bgv": (i32, [vp, i32, i32, i32, u64, C.POINTER(vp)]),
     "b200fhe_keyswitch_destroy": (i32, [vp]),
     "b200fhe_keyswitch_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(sz)]),
     "b200fhe_keyswitch_modup": (i32, [vp, vp, vp, vp]),
@@ -243,11 +245,12 @@ Context.pmult_accum = _pmult_accum
 class BaseConv:
     """ModUp plan (b200fhe_bconv): source base = context moduli src_idx, targets = context moduli dst_idx."""
 
-    def __init__(self, ctx, src_idx, dst_idx):
+    def __init__(self, ctx, src_idx, dst_idx, scale=1):
         self.ctx, self.src, self.dst = ctx, list(src_idx), list(dst_idx)
         self.m, self.K, self.N = len(self.src), len(self.dst), ctx.N
         h = vp()
-        check(lib().b200fhe_bconv_create(ctx._h, (i32 * self.m)(*self.src), self.m, (i32 * self.K)(*self.dst), self.K, C.byref(h)))
+        check(lib().b200fhe_bconv_create_scaled(ctx._h, (i32 * self.m)(*self.src), self.m, (i32 * self.K)(*self.dst), self.K, scale,
+                                                C.byref(h)))
         self._h = h
 
     def close(self):
@@ -308,10 +311,10 @@ class KeySwitch:
     """Hybrid key-switch plan (b200fhe_keyswitch): ctx holds n_q ciphertext moduli then n_p special primes.
     Device pointers in and out (torch tensors' data_ptr()); shapes in include/b200fhe.h."""
 
-    def __init__(self, ctx, n_q, n_p, dnum):
+    def __init__(self, ctx, n_q, n_p, dnum, plain_modulus=1):
         self.ctx, self.n_q, self.n_p, self.dnum, self.N = ctx, n_q, n_p, dnum, ctx.N
         h = vp()
-        check(lib().b200fhe_keyswitch_create(ctx._h, n_q, n_p, dnum, C.byref(h)))
+        check(lib().b200fhe_keyswitch_create_bgv(ctx._h, n_q, n_p, dnum, plain_modulus, C.byref(h)))
         self._h = h
 
     def close(self):

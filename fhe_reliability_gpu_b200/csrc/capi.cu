@@ -625,7 +625,14 @@ extern "C" int b200fhe_bconv_destroy(b200fhe_bconv* p) {
 }
 
 extern "C" int b200fhe_bconv_create(b200fhe_ctx* c, const int* src_idx, int m, const int* dst_idx, int K, b200fhe_bconv** out) {
-    if (!c || !src_idx || !dst_idx || !out || m < 1 || K < 1 || m > 64) return b200_set_err(B200FHE_EINVAL, "bconv_create: bad arguments");
+    return b200fhe_bconv_create_scaled(c, src_idx, m, dst_idx, K, 1, out);
+}
+
+// t > 1: the conversion returns t * [x t^-1]_P (+ e t P): congruent to x modulo P and to 0 modulo t -- what BGV's ModDown /
+// mod-switch subtract so that the division by P leaves the plaintext (mod t) intact.  t = 1: plain HPS conversion.
+extern "C" int b200fhe_bconv_create_scaled(b200fhe_ctx* c, const int* src_idx, int m, const int* dst_idx, int K, uint64_t t,
+                                           b200fhe_bconv** out) {
+    if (!c || !src_idx || !dst_idx || !out || m < 1 || K < 1 || m > 64 || t < 1) return b200_set_err(B200FHE_EINVAL, "bconv_create: bad arguments");
     std::vector<u32> src(m), dst(K);
     for (int j = 0; j < m; j++) {
         if (src_idx[j] < 0 || src_idx[j] >= c->L || !c->moduli[src_idx[j]]) return b200_set_err(B200FHE_EINVAL, "bconv_create: bad source index %d", src_idx[j]);
@@ -644,13 +651,15 @@ extern "C" int b200fhe_bconv_create(b200fhe_ctx* c, const int* src_idx, int m, c
         uint64_t h = 1;
         for (int i = 0; i < m; i++)
             if (i != j) h = nt::mulmod(h, c->moduli[src[i]] % pj, pj);
-        const uint64_t iv = nt::invmod(h, pj);
+        if (t % pj == 0) return b200_set_err(B200FHE_EINVAL, "bconv_create: scale %llu is not invertible modulo source modulus %d", (unsigned long long)t, src_idx[j]);
+        const uint64_t iv = nt::invmod(nt::mulmod(h, t % pj, pj), pj);
         inv[j] = make_ulonglong2(iv, nt::shoup(iv, pj));
         for (int k = 0; k < K; k++) {
             const uint64_t qk = c->moduli[dst[k]];
             uint64_t g = 1;
             for (int i = 0; i < m; i++)
                 if (i != j) g = nt::mulmod(g, c->moduli[src[i]] % qk, qk);
+            g = nt::mulmod(g, t % qk, qk);
             hat[(size_t)k * m + j] = (g & 0x3fffffffull) | ((g >> 30) << 32);
             raw[(size_t)k * m + j] = g;
         }

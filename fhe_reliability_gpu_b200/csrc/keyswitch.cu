@@ -85,6 +85,13 @@ extern "C" int b200fhe_keyswitch_destroy(b200fhe_keyswitch* k) {
 }
 
 extern "C" int b200fhe_keyswitch_create(b200fhe_ctx* c, int n_q, int n_p, int dnum, b200fhe_keyswitch** out) {
+    return b200fhe_keyswitch_create_bgv(c, n_q, n_p, dnum, 1, out);
+}
+
+// plain_modulus t > 1: BGV flavour -- ModDown subtracts t [acc t^-1]_P instead of [acc]_P, so the quotient differs from
+// acc / P by a multiple of t only and the plaintext survives (switching keys then carry t e_d as their noise term).
+extern "C" int b200fhe_keyswitch_create_bgv(b200fhe_ctx* c, int n_q, int n_p, int dnum, uint64_t plain_modulus, b200fhe_keyswitch** out) {
+    if (plain_modulus < 1) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: plain modulus must be >= 1");
     if (!c || !out || n_q < 1 || n_p < 1 || dnum < 0) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: bad arguments");
     if (n_q + n_p != c->L) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: context holds %d moduli, need n_q + n_p = %d", c->L, n_q + n_p);
     if (dnum && n_q % dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_create: n_q=%d not divisible by dnum=%d", n_q, dnum);
@@ -109,7 +116,7 @@ extern "C" int b200fhe_keyswitch_create(b200fhe_ctx* c, int n_q, int n_p, int dn
         std::vector<int> src, dst;
         for (int g = n_q; g < total; g++) src.push_back(g);
         for (int g = 0; g < n_q; g++) dst.push_back(g);
-        rc = b200fhe_bconv_create(c, src.data(), n_p, dst.data(), n_q, &k->down);
+        rc = b200fhe_bconv_create_scaled(c, src.data(), n_p, dst.data(), n_q, plain_modulus, &k->down);
     }
     if (rc) {
         b200fhe_keyswitch_destroy(k);

@@ -14,12 +14,14 @@ from . import binding as B
 
 
 class Evaluator:
-    def __init__(self, ctx, n_q, n_p, dnum):
-        """ctx: Context over n_q ciphertext moduli followed by n_p special primes."""
+    def __init__(self, ctx, n_q, n_p, dnum, plain_modulus=1):
+        """ctx: Context over n_q ciphertext moduli followed by n_p special primes.  plain_modulus t > 1 selects the BGV
+        flavour of ModDown / rescale (the subtracted term is made a multiple of t, so plaintexts mod t survive)."""
         import torch
         self.torch = torch
         self.ctx, self.n_q, self.n_p, self.dnum, self.N = ctx, n_q, n_p, dnum, ctx.N
-        self.ks = B.KeySwitch(ctx, n_q, n_p, dnum)
+        self.t = plain_modulus
+        self.ks = B.KeySwitch(ctx, n_q, n_p, dnum, plain_modulus)
         self._rescale = None
 
     def _stream(self):
@@ -77,11 +79,13 @@ class Evaluator:
         return out
 
     def rescale_to_next(self, ct, q_ctx):
-        """Drop the last ciphertext prime: [size][n_q][N] -> [size][n_q - 1][N] = floor(ct / q_last) (no rounding term).
+        """Drop the last ciphertext prime: [size][n_q][N] -> [size][n_q - 1][N] = floor(ct / q_last) (no rounding term);
+        with a plain modulus t: (ct - t [ct t^-1]_q_last) / q_last, BGV's mod_switch_to_next (the plaintext becomes
+        m q_last^-1 mod t, the correction factor BGV libraries track).
         q_ctx: a Context over exactly the n_q ciphertext moduli (the last one plays the special prime of a ModDown)."""
         self._check(ct)
         if self._rescale is None or self._rescale[0] is not q_ctx:
-            self._rescale = (q_ctx, B.KeySwitch(q_ctx, self.n_q - 1, 1, 0))
+            self._rescale = (q_ctx, B.KeySwitch(q_ctx, self.n_q - 1, 1, 0, self.t))
         plan = self._rescale[1]
         size, nq1 = ct.shape[0], self.n_q - 1
         out = self.torch.empty((size, nq1, self.N), dtype=self.torch.int64, device=ct.device)

@@ -199,6 +199,10 @@ typedef struct b200fhe_bconv b200fhe_bconv;
  * run (reliability_test/dotprod_test.cu:114,146); in-tree spec rfhe_framewk/src/baseConv.py:10-40:
  *   y_j = x_j (P/p_j)^-1 mod p_j ;  out_k = sum_j y_j ((P/p_j) mod q_k) mod q_k      (= x + e P, 0 <= e < m). */
 int b200fhe_bconv_create(b200fhe_ctx* ctx, const int* src_idx, int m, const int* dst_idx, int K, b200fhe_bconv** out);
+/* Same with a scale t >= 1 folded into the constants: out = t [x t^-1]_P (+ e t P), congruent to x mod P and to 0 mod t
+ * (BGV ModDown / mod_switch_to_next subtract this so the plaintext mod t survives the division by P); t = 1 is the plain
+ * conversion.  t must be invertible modulo every source modulus. */
+int b200fhe_bconv_create_scaled(b200fhe_ctx* ctx, const int* src_idx, int m, const int* dst_idx, int K, uint64_t t, b200fhe_bconv** out);
 int b200fhe_bconv_destroy(b200fhe_bconv* plan);
 
 /* Step 1 on `count` source limbs starting at source position j0: d_y[c][i] = d_x[c][i] (P/p_j)^-1 mod p_j,
@@ -242,6 +246,9 @@ int b200fhe_bconv_modup_protected_host(b200fhe_bconv* plan, const uint64_t* h_in
  * synchronisation), so a switch can be captured in a CUDA graph. */
 typedef struct b200fhe_keyswitch b200fhe_keyswitch;
 int b200fhe_keyswitch_create(b200fhe_ctx* ctx, int n_q, int n_p, int dnum, b200fhe_keyswitch** out);
+/* BGV flavour: ModDown with the plaintext-modulus correction (subtracts t [acc t^-1]_P); plain_modulus = 1 is
+ * b200fhe_keyswitch_create. */
+int b200fhe_keyswitch_create_bgv(b200fhe_ctx* ctx, int n_q, int n_p, int dnum, uint64_t plain_modulus, b200fhe_keyswitch** out);
 /* dnum = 0 makes a ModDown-only plan (no ModUp tables or workspace): with n_p = 1 its b200fhe_keyswitch_moddown is
  * rescale_to_next / the division step of mod_switch_to_next (dotprod_test.cu:115: drop the last prime q_last,
  * out_l = (c_l - [c]_q_last) q_last^-1 mod q_l = floor(c / q_last), no rounding term). */

@@ -262,11 +262,22 @@ def keyswitch_modup(c, moduli, n_q, n_p, dnum, tabs):
     return up
 
 
-def keyswitch_moddown(acc, moduli, n_q, n_p, tabs):
-    """acc [n_q+n_p][N] NTT domain -> [n_q][N]: (acc - BaseConv_{P->Q}(acc mod P)) * P^-1 mod q_l."""
+def bconv_hps_scaled(x, p, qo, t=1):
+    """t [x t^-1]_P (+ e t P) mod qo_k: the HPS conversion with a scale folded in (== t * bconv_hps(x t^-1 mod p_j))."""
+    if t == 1:
+        return bconv_hps(x, p, qo)
+    x = np.ascontiguousarray(x, dtype=np.uint64)
+    xs = np.stack([np.array((x[j].astype(object) * pow(int(t), -1, int(pj))) % int(pj), dtype=np.uint64) for j, pj in enumerate(p)])
+    out = bconv_hps(xs, p, qo)
+    return np.stack([np.array((out[k].astype(object) * int(t)) % int(qk), dtype=np.uint64) for k, qk in enumerate(qo)])
+
+
+def keyswitch_moddown(acc, moduli, n_q, n_p, tabs, t=1):
+    """acc [n_q+n_p][N] NTT domain -> [n_q][N]: (acc - BaseConv_{P->Q}(acc mod P)) * P^-1 mod q_l.  t > 1: BGV flavour,
+    the subtracted term is t [acc t^-1]_P (congruent to acc mod P, to 0 mod t)."""
     acc = np.ascontiguousarray(acc, dtype=np.uint64)
-    t = ntt_inverse_batch(acc[n_q:], tabs[n_q:])
-    conv = ntt_forward_batch(bconv_hps(t, moduli[n_q:], moduli[:n_q]), tabs[:n_q])
+    tt = ntt_inverse_batch(acc[n_q:], tabs[n_q:])
+    conv = ntt_forward_batch(bconv_hps_scaled(tt, moduli[n_q:], moduli[:n_q], t), tabs[:n_q])
     out = np.zeros((n_q, acc.shape[1]), dtype=np.uint64)
     P = 1
     for p in moduli[n_q:]:
@@ -279,11 +290,11 @@ def keyswitch_moddown(acc, moduli, n_q, n_p, tabs):
     return out
 
 
-def keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs):
-    """c [n_q][N]; evk [dnum][2][n_q+n_p][N]; returns [2][n_q][N] (all NTT domain)."""
+def keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs, t=1):
+    """c [n_q][N]; evk [dnum][2][n_q+n_p][N]; returns [2][n_q][N] (all NTT domain).  t: plain modulus (BGV) or 1."""
     up = keyswitch_modup(c, moduli, n_q, n_p, dnum, tabs)
     acc = pmult_accum(np.ascontiguousarray(evk, dtype=np.uint64), up, moduli)       # terms = digits, "plaintext" = up_d
-    return np.stack([keyswitch_moddown(acc[p], moduli, n_q, n_p, tabs) for p in range(2)])
+    return np.stack([keyswitch_moddown(acc[p], moduli, n_q, n_p, tabs, t) for p in range(2)])
 
 
 # ---------------------------------------------------------------- checksum-carrying base conversion (SURVEY 8f row f2)

@@ -12,9 +12,9 @@ def _neg(a, moduli):
     return (q - a) % q
 
 
-def make_switch_key(O, rng, s, s_new, moduli, n_q, n_p, dnum, tabs, sigma=3.2):
+def make_switch_key(O, rng, s, s_new, moduli, n_q, n_p, dnum, tabs, sigma=3.2, t=1):
     """evk_d = (-a_d s + e_d + P B_d s_new, a_d) over Q u P, NTT domain; B_d = 1 mod the digit's moduli, 0 mod the rest of Q.
-    Modular products through the oracle's pmult (C), so full-size keys take seconds."""
+    Modular products through the oracle's pmult (C), so full-size keys take seconds.  t > 1: BGV keys (noise term t e_d)."""
     N = len(s)
     alpha = n_q // dnum
     P = 1
@@ -25,7 +25,7 @@ def make_switch_key(O, rng, s, s_new, moduli, n_q, n_p, dnum, tabs, sigma=3.2):
     evk = np.zeros((dnum, 2, n_q + n_p, N), dtype=np.uint64)
     for d in range(dnum):
         a = O.uniform_limbs(moduli, N, seed=int(rng.integers(1 << 30)))
-        e = _ntt_small(O, np.rint(rng.normal(0, sigma, N)).astype(np.int64), moduli, tabs)
+        e = _ntt_small(O, np.rint(rng.normal(0, sigma, N)).astype(np.int64) * int(t), moduli, tabs)
         factor = np.zeros_like(a)                                   # P B_d mod q_l (0 mod every p_j as well)
         for l in range(d * alpha, (d + 1) * alpha):
             factor[l, :] = P % int(moduli[l])

@@ -146,3 +146,36 @@ def test_rotate_decrypts_to_the_automorphed_plaintext(pkg, O, log_n, n_q, n_p, d
     dec = O.ntt_inverse_batch(O.pmult_accum(ct[:, None], np.stack([ones, s_h]), qs)[0], tq)        # m + e, coefficient domain
     dec_g = np.stack([O.ntt_forward(O.galois_coeff(dec[l], g, int(qs[l])), tq[l]) for l in range(n_q)])
     _residual(O, [out[0], out[1], _neg(dec_g, qs)], [ones, s_h, ones], qs, tq, 34)
+
+
+def test_bgv_mod_switch_keeps_the_plaintext_up_to_the_correction_factor(pkg, O):
+    """BGV: ct = (-a s + t e + m, a); after mod_switch_to_next (rescale with plain_modulus = t) the ciphertext decrypts
+    EXACTLY to m q_last^-1 mod t -- the correction factor BGV libraries track (Phantom / SEAL mod_switch_to_next)."""
+    import torch
+    from fhe_reliability_gpu_b200.evaluator import Evaluator
+    log_n, L, t = 10, 4, 65537
+    N = 1 << log_n
+    moduli = pkg.primes_create(N, [60] * (L + 1))
+    ctx = pkg.Context(log_n, moduli)
+    q_ctx = pkg.Context(log_n, moduli[:L])
+    tabs = [O.Tables(log_n, q) for q in moduli]
+    ev = Evaluator(ctx, L, 1, 1, plain_modulus=t)
+    qs, tq = moduli[:L], tabs[:L]
+    rng = np.random.default_rng(2)
+    s = rng.integers(-1, 2, N)
+    s_h = _ntt_small(O, s, qs, tq)
+    m = rng.integers(0, t, N)
+    a = O.uniform_limbs(qs, N, seed=5)
+    me = _ntt_small(O, np.asarray(m) + t * np.rint(rng.normal(0, 3.2, N)).astype(np.int64), qs, tq)
+    c0 = O.pmult_accum(np.stack([_neg(a, qs), me])[:, None], np.stack([s_h, np.ones_like(s_h)]), qs)[0]
+    out = _host(ev.rescale_to_next(_dev(torch, np.stack([c0, a])), q_ctx))
+    lo, tl = qs[:L - 1], tq[:L - 1]
+    dec = O.ntt_inverse_batch(O.pmult_accum(out[:, None], np.stack([np.ones_like(s_h[:L - 1]), s_h[:L - 1]]), lo)[0], tl).astype(np.int64)
+    q = np.array([int(v) for v in lo], dtype=np.int64)[:, None]
+    dec = np.where(dec > q // 2, dec - q, dec)
+    assert (dec == dec[0]).all() and np.abs(dec).max() < 1 << 40
+    want = (m.astype(object) * pow(int(moduli[L - 1]), -1, t)) % t
+    assert [int(v) % t for v in dec[0]] == [int(v) for v in want]
+    # bit-exact against the oracle's t-scaled ModDown
+    for p, poly in enumerate((c0, a)):
+        assert np.array_equal(out[p], O.keyswitch_moddown(poly, qs, L - 1, 1, tq, t=t))

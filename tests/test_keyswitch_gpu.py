@@ -98,3 +98,25 @@ def test_keyswitch_argument_errors(pkg):
     assert ks.workspace_bytes() > 0
     with pytest.raises(pkg.B200FHEError):
         ks.apply(0, 0, 0, 0)
+
+
+@pytest.mark.parametrize("log_n,n_q,n_p,dnum,t", [(10, 6, 2, 3, 65537), (12, 4, 4, 1, 1032193), (13, 8, 4, 2, 65537)])
+def test_bgv_keyswitch_parity_and_plaintext_modulus(pkg, O, log_n, n_q, n_p, dnum, t):
+    """plain_modulus = t: bit-exact with the oracle's t-scaled composition, and the residual out0 + out1 s - c s' is a
+    small multiple of t (the plaintext mod t is untouched by the switch)."""
+    import torch
+    N, moduli, ctx, tabs = _setup(pkg, O, log_n, n_q, n_p)
+    rng = np.random.default_rng(log_n + dnum)
+    s, s_new = rng.integers(-1, 2, N), rng.integers(-1, 2, N)
+    evk = make_switch_key(O, rng, s, s_new, moduli, n_q, n_p, dnum, tabs, t=t)
+    c = O.uniform_limbs(moduli[:n_q], N, seed=21)
+    ks = pkg.KeySwitch(ctx, n_q, n_p, dnum, plain_modulus=t)
+    eq, ep = _split(evk, n_q)
+    d_c, d_eq, d_ep = _dev(torch, c), _dev(torch, eq), _dev(torch, ep)
+    d_out = torch.zeros((2, n_q, N), dtype=torch.int64, device="cuda")
+    ks.apply(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr())
+    torch.cuda.synchronize()
+    out = _host(d_out)
+    assert np.array_equal(out, O.keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs, t=t))
+    noise = check_switch_noise(O, out, c, s, s_new, moduli[:n_q], tabs[:n_q], bound_bits=44)
+    assert not (noise % t).any()

@@ -43,3 +43,19 @@ def test_oracle_modup_raises_digit_exactly_up_to_small_multiple(O):
                 xi = (xi + int(x[g, i]) * pow(Dg, -1, int(moduli[g])) % int(moduli[g]) * Dg) % D
             es = {e for e in range(alpha) if all((xi + e * D) % int(moduli[g]) == int(coeff[g, i]) for g in range(n_q + n_p))}
             assert len(es) == 1
+
+
+def test_oracle_bgv_keyswitch_keeps_the_plaintext_modulus(O):
+    """BGV flavour (t-scaled ModDown, keys with noise t e_d): out0 + out1 s - c s' is small AND a multiple of t."""
+    log_n, n_q, n_p, dnum, t = 8, 6, 2, 3, 65537
+    N = 1 << log_n
+    moduli = O.primes_create(N, [50] * (n_q + n_p))
+    tabs = [O.Tables(log_n, q) for q in moduli]
+    rng = np.random.default_rng(12)
+    s, s_new = rng.integers(-1, 2, N), rng.integers(-1, 2, N)
+    evk = make_switch_key(O, rng, s, s_new, moduli, n_q, n_p, dnum, tabs, t=t)
+    c = O.uniform_limbs(moduli[:n_q], N, seed=3)
+    noise = check_switch_noise(O, O.keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs, t=t), c, s, s_new, moduli[:n_q], tabs[:n_q], 40)
+    assert not (noise % t).any() and np.abs(noise).max() > 0
+    plain = check_switch_noise(O, O.keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs), c, s, s_new, moduli[:n_q], tabs[:n_q], 40)
+    assert (plain % t).any()                      # without the correction the residual is not a multiple of t
