@@ -71,7 +71,16 @@ def main():
     ks.apply(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr(), stream=sp)
     torch.cuda.synchronize()
     launches = int(pkg.lib().b200fhe_launch_count() - launches0)
+    cpu_baseline = None
     if not args.no_check:
+        import time
+        t0 = time.perf_counter()
+        want = O.keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs)          # the CPU restatement, timed beside the GPU path
+        dt = time.perf_counter() - t0
+        if not np.array_equal(want, d_out.cpu().numpy().view(np.uint64)):
+            raise SystemExit("key-switch differs from the oracle composition")
+        cpu_baseline = {"value": 1.0 / dt, "unit": "key-switches/s", "cores": os.cpu_count(), "kind": "port",
+                        "sample": "one key-switch of the same shape (oracle: OpenMP NTT batches + C base conversion / multiply-accumulate)"}
         noise = check_switch_noise(O, d_out.cpu().numpy().view(np.uint64), c, s, s_new, moduli[:n_q], tabs[:n_q])
         parity = "out0 + out1 s - c s' is one integer polynomial with max |coeff| = %d (RLWE key, sigma 3.2)" % int(np.abs(noise).max())
 
@@ -138,7 +147,7 @@ def main():
         "roofline": {"bound": "integer multiplier pipe (NTT butterflies + dense base-conversion contraction); HBM shown for scale",
                      "hbm_achieved_GBs": words * 8 / (ms * 1e-3) / 1e9, "hbm_peak_GBs": peak,
                      "limb_transforms_per_s": transforms / (ms * 1e-3)},
-        "parity": parity}))
+        "parity": parity + ("; bit-exact against the oracle composition" if cpu_baseline else ""), "cpu_baseline": cpu_baseline}))
 
 
 if __name__ == "__main__":

@@ -278,16 +278,15 @@ def keyswitch_moddown(acc, moduli, n_q, n_p, tabs, t=1):
     acc = np.ascontiguousarray(acc, dtype=np.uint64)
     tt = ntt_inverse_batch(acc[n_q:], tabs[n_q:])
     conv = ntt_forward_batch(bconv_hps_scaled(tt, moduli[n_q:], moduli[:n_q], t), tabs[:n_q])
-    out = np.zeros((n_q, acc.shape[1]), dtype=np.uint64)
     P = 1
     for p in moduli[n_q:]:
         P *= int(p)
-    for l in range(n_q):
-        q = int(moduli[l])
-        pinv = pow(P % q, -1, q)
-        d = (acc[l].astype(object) - conv[l].astype(object)) % q
-        out[l] = np.array((d * pinv) % q, dtype=np.uint64)
-    return out
+    N = acc.shape[1]
+    qa = np.array([int(q) for q in moduli[:n_q]], dtype=np.uint64)[:, None]
+    pinv = np.stack([np.full(N, pow(P % int(q), -1, int(q)), dtype=np.uint64) for q in moduli[:n_q]])
+    neg = (qa - conv) % qa
+    # (acc - conv) * P^-1 = acc * pinv + (q - conv) * pinv, through the C multiply-accumulate
+    return pmult_accum(np.stack([acc[:n_q], neg])[:, None], np.stack([pinv, pinv]), moduli[:n_q])[0]
 
 
 def keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs, t=1):
