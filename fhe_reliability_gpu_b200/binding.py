@@ -57,6 +57,8 @@ SIGNATURES = {
     "b200fhe_keyswitch_modup": (i32, [vp, vp, vp, vp]),
     "b200fhe_keyswitch_moddown": (i32, [vp, vp, vp, vp, sz, vp]),
     "b200fhe_keyswitch_apply": (i32, [vp, vp, vp, vp, vp, vp]),
+    "b200fhe_keyswitch_apply_protected": (i32, [vp, vp, vp, vp, vp, vp, vp]),
+    "b200fhe_keyswitch_set_inject": (i32, [vp, i32, vp, sz]),
     "b200fhe_ct_tensor": (i32, [vp, vp, vp, vp, sz, sz, vp]),
     "b200fhe_poly_add": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "b200fhe_poly_sub": (i32, [vp, vp, vp, sz, sz, sz, vp]),
@@ -337,6 +339,17 @@ class KeySwitch:
 
     def apply(self, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, stream=0):
         check(lib().b200fhe_keyswitch_apply(self._h, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, stream))
+
+    def set_inject(self, conversion, inject):
+        """arm (stage, limb, coeff, xor_mask) faults for the next apply_protected; conversion: digit index, or dnum / dnum+1 for ModDown"""
+        arr = (BconvInject * max(len(inject), 1))()
+        for i, e in enumerate(inject):
+            arr[i] = BconvInject(*[int(v) for v in e])
+        check(lib().b200fhe_keyswitch_set_inject(self._h, conversion, C.cast(arr, vp), len(inject)))
+
+    def apply_protected(self, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, verdict_ptr, stream=0):
+        """verdict: uint32 [dnum + 2][n_q + n_p] on the device; all zero = every conversion check passed."""
+        check(lib().b200fhe_keyswitch_apply_protected(self._h, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, verdict_ptr, stream))
 
 
 def flip_bit(ptr, idx, bit, stream=0):

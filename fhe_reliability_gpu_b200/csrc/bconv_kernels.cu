@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(kTcWarps * 32, 2)
                 a[mt][s][3] = (j1 < m && r1 < N) ? __ldg(y32 + ((size_t)j1 * N + r1) * 2 + (t & 1)) : 0;
             }
         }
-        if (PROT && blockIdx.y == 0) {
+        if (PROT && blockIdx.y == 0 && cin) {
             // every (source limb, row, half) is held by exactly one fragment register of the warp: a[.][s][r] is the
             // (t & 1) half of y[4s + (t >> 1) + 2 (r >> 1)][row]; rows >= N and limbs >= m were loaded as 0
 #pragma unroll
@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(kTcWarps * 32, 2)
 #pragma unroll
                 for (int w8 = 0; w8 < kTcWarps; w8++) v += so[(size_t)w8 * kc * 2 + k];
                 red_add64(cout + (size_t)ka * 2 + k, v);
-            } else if (blockIdx.y == 0) {
+            } else if (blockIdx.y == 0 && cin) {
                 const u32 e = k - 2 * kc;
 #pragma unroll
                 for (int w8 = 0; w8 < kTcWarps; w8++) v += si[w8 * 32 + e];
@@ -485,9 +485,12 @@ __global__ void k_bconv_xor(u64* y, size_t idx, u64 mask) { y[idx] ^= mask; }
 
 // Protected ModUp of one digit on one GPU: scale -> [memory-fault injection] -> contraction -> finalize.
 // inj: host array of n_inj entries {stage, limb, coeff, mask}; stage 1 = scale product, 2 = contraction output, 3 = y in memory.
+// out_hi != nullptr: targets [0, k_split) go to out, targets [k_split, K) to out_hi (the key-switch writes the targets below and
+// above a digit's own limbs into different rows); the second launch does not count the input sums again.
 int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
                                  const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
-                                 u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches) {
+                                 u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches,
+                                 u64* out_hi, u32 k_split) {
     if (!btab || m > 16 || n_inj > (u32)kBconvMaxInj) return -1;
     BconvInjList il;
     il.n = n_inj;
@@ -500,7 +503,16 @@ int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* 
             k_bconv_xor<<<1, 1, 0, s>>>(y, (size_t)il.e[e].limb * N + il.e[e].coeff, il.e[e].mask);
             nl++;
         }
-    int rc = launch_tc_ks<true>(y, out, mods, dst_idx, btab, N, m, K, 0, K, s, counters + (size_t)4 * m, counters + (size_t)6 * m, il);
+    u64* cin = counters + (size_t)4 * m;
+    u64* cout = counters + (size_t)6 * m;
+    int rc;
+    if (out_hi && k_split < K) {
+        rc = k_split ? launch_tc_ks<true>(y, out, mods, dst_idx, btab, N, m, K, 0, k_split, s, cin, cout, il) : 0;
+        if (!rc) rc = launch_tc_ks<true>(y, out_hi, mods, dst_idx, btab, N, m, K, k_split, K - k_split, s, k_split ? nullptr : cin, cout, il);
+        nl += k_split ? 1 : 0;
+    } else {
+        rc = launch_tc_ks<true>(y, out, mods, dst_idx, btab, N, m, K, 0, K, s, cin, cout, il);
+    }
     if (rc) return rc;
     k_bconv_prot_finalize<<<(m + K + 3) / 4, 128, 0, s>>>(counters, next_counters, mods, src_idx, dst_idx, inv, hat, m, K, verdict, sums);
     if (launches) *launches += nl + 2;

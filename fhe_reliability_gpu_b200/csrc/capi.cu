@@ -759,9 +759,18 @@ extern "C" int b200fhe_bconv_modup_host(b200fhe_bconv* p, const uint64_t* h_in, 
     return 0;
 }
 
+int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_y, uint64_t* d_out, uint64_t* d_out_hi, size_t k_split,
+                                     uint32_t* d_verdict, uint64_t* d_sums, const b200fhe_bconv_inject* inject, size_t n_inject, void* stream);
+
 extern "C" int b200fhe_bconv_modup_protected(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_out, uint32_t* d_verdict, uint64_t* d_sums,
                                              const b200fhe_bconv_inject* inject, size_t n_inject, void* stream) {
-    if (!p || !d_in || !d_out || !d_verdict) return b200_set_err(B200FHE_EINVAL, "bconv_modup_protected: null argument");
+    return b200_bconv_modup_protected_split(p, d_in, p ? (uint64_t*)p->d_y : nullptr, d_out, nullptr, 0, d_verdict, d_sums, inject, n_inject, stream);
+}
+
+// shared with keyswitch.cu: scaled digit into d_y, targets [0, k_split) into d_out and the rest into d_out_hi (or all into d_out)
+int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_y, uint64_t* d_out, uint64_t* d_out_hi, size_t k_split,
+                                     uint32_t* d_verdict, uint64_t* d_sums, const b200fhe_bconv_inject* inject, size_t n_inject, void* stream) {
+    if (!p || !d_in || !d_y || !d_out || !d_verdict) return b200_set_err(B200FHE_EINVAL, "bconv_modup_protected: null argument");
     if (n_inject > B200FHE_BCONV_MAX_INJECT || (n_inject && !inject)) return b200_set_err(B200FHE_EINVAL, "bconv_modup_protected: bad injection plan");
     if (!p->d_btab) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup_protected: needs the tensor-core plan (at most 16 source moduli)");
     CK(cudaSetDevice(p->ctx->device));
@@ -775,9 +784,9 @@ extern "C" int b200fhe_bconv_modup_protected(b200fhe_bconv* p, const uint64_t* d
     u64* nxt = p->d_cnt + (size_t)(p->cnt_set ^ 1) * n_cnt;
     p->cnt_set ^= 1;
     static_assert(sizeof(b200fhe_bconv_inject) == 24, "layout shared with BconvInj");
-    int rc = launch_bconv_modup_protected((const u64*)d_in, p->d_y, (u64*)d_out, p->ctx->d_mods, p->d_src, p->d_dst, p->d_inv, p->d_hat, p->d_btab,
+    int rc = launch_bconv_modup_protected((const u64*)d_in, (u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_src, p->d_dst, p->d_inv, p->d_hat, p->d_btab,
                                           (u32)p->ctx->N, (u32)p->m, (u32)p->K, cur, nxt, d_verdict, (u64*)d_sums, inject, (u32)n_inject,
-                                          (cudaStream_t)stream, &g_launches);
+                                          (cudaStream_t)stream, &g_launches, (u64*)d_out_hi, (u32)k_split);
     if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup_protected: unsupported plan");
     CK(cudaGetLastError());
     return 0;

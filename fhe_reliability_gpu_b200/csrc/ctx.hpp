@@ -60,7 +60,8 @@ int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const 
 // checksum-carrying ModUp of one digit (scale + tensor-core contraction + finalize); counters: 6 m + 2 K words of scratch
 int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
                                  const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
-                                 u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches);
+                                 u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches,
+                                 u64* out_hi = nullptr, u32 k_split = 0);
 
 }  // namespace b200
 

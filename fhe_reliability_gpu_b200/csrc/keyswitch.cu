@@ -47,6 +47,9 @@ struct b200fhe_keyswitch {
     ulonglong2* d_pinv = nullptr;        // [n_q] (P^-1 mod q_l, Shoup quotient)
     uint64_t* d_ws = nullptr;                 // workspace, see offsets
     size_t o_x = 0, o_y = 0, o_up = 0, o_accq = 0, o_accp = 0, o_conv = 0, ws_words = 0;
+    // fault injection armed for the next protected apply (b200fhe_keyswitch_set_inject)
+    int inj_conv = -1;
+    std::vector<b200fhe_bconv_inject> inj;
 };
 
 namespace b200 {
@@ -152,7 +155,12 @@ extern "C" int b200fhe_keyswitch_create_bgv(b200fhe_ctx* c, int n_q, int n_p, in
 }
 
 // steps 1-2: every digit of c raised to the full basis, NTT domain.  d_up [dnum][n_q + n_p][N].
-extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, void* stream) {
+int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_y, uint64_t* d_out, uint64_t* d_out_hi, size_t k_split,
+                                     uint32_t* d_verdict, uint64_t* d_sums, const b200fhe_bconv_inject* inject, size_t n_inject, void* stream);
+
+// verdict (optional): [dnum][n_q + n_p] checksum verdicts of the digits' conversions (b200fhe_bconv_modup_protected layout:
+// alpha source-limb entries, then the targets)
+static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, uint32_t* verdict, void* stream) {
     if (!k || !d_c || !d_up) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: null argument");
     if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
@@ -172,20 +180,30 @@ extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c
         const uint64_t* xd = x + (size_t)d * a * N;
         uint64_t* yd = y + (size_t)d * a * N;
         uint64_t* upd = (uint64_t*)d_up + (size_t)d * total * N;
-        RC(b200fhe_bconv_scale(p, xd, yd, 0, a, stream));
         const size_t below = (size_t)d * a, above = total - below - a;
-        RC(b200fhe_bconv_contract(p, yd, upd, 0, below, stream));
-        RC(b200fhe_bconv_contract(p, yd, upd + (below + a) * N, below, above, stream));
+        if (verdict) {
+            const bool hit = k->inj_conv == d;
+            RC(b200_bconv_modup_protected_split(p, xd, yd, upd, upd + (below + a) * N, below, verdict + (size_t)d * total, nullptr,
+                                                hit ? k->inj.data() : nullptr, hit ? k->inj.size() : 0, stream));
+        } else {
+            RC(b200fhe_bconv_scale(p, xd, yd, 0, a, stream));
+            RC(b200fhe_bconv_contract(p, yd, upd, 0, below, stream));
+            RC(b200fhe_bconv_contract(p, yd, upd + (below + a) * N, below, above, stream));
+        }
         if (below) RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
         RC(b200fhe_nwt_forward(c, upd + (below + a) * N, 1, above, below + a, stream));
     }
     return 0;
 }
 
+extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, void* stream) {
+    return modup_impl(k, d_c, d_up, nullptr, stream);
+}
+
 // step 4 for n_poly polynomials: d_acc_q [n_poly][n_q][N], d_acc_p [n_poly][n_p][N] (overwritten), d_out [n_poly][n_q][N]
 // (may alias d_acc_q).  n_poly <= 2.
-extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out,
-                                         size_t n_poly, void* stream) {
+static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out, size_t n_poly,
+                        uint32_t* verdict /*optional [n_poly][n_p + n_q]*/, void* stream) {
     if (!k || !d_acc_q || !d_acc_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: null argument");
     if (n_poly < 1 || n_poly > 2) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: n_poly must be 1 or 2");
     b200fhe_ctx* c = k->ctx;
@@ -196,8 +214,14 @@ extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d
     uint64_t* conv = k->d_ws + k->o_conv;
     RC(b200fhe_nwt_backward(c, d_acc_p, n_poly, np, nq, stream));
     for (size_t p = 0; p < n_poly; p++) {
-        RC(b200fhe_bconv_scale(k->down, d_acc_p + p * np * N, y + p * np * N, 0, np, stream));
-        RC(b200fhe_bconv_contract(k->down, y + p * np * N, conv + p * nq * N, 0, nq, stream));
+        if (verdict) {
+            const bool hit = k->inj_conv == k->dnum + (int)p;
+            RC(b200_bconv_modup_protected_split(k->down, d_acc_p + p * np * N, y + p * np * N, conv + p * nq * N, nullptr, 0,
+                                                verdict + p * (np + nq), nullptr, hit ? k->inj.data() : nullptr, hit ? k->inj.size() : 0, stream));
+        } else {
+            RC(b200fhe_bconv_scale(k->down, d_acc_p + p * np * N, y + p * np * N, 0, np, stream));
+            RC(b200fhe_bconv_contract(k->down, y + p * np * N, conv + p * nq * N, 0, nq, stream));
+        }
     }
     RC(b200fhe_nwt_forward(c, conv, n_poly, nq, 0, stream));
     dim3 grid((unsigned)((N / 2 + 255) / 256), (unsigned)nq, (unsigned)n_poly);
@@ -207,10 +231,15 @@ extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d
     return 0;
 }
 
+extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out,
+                                         size_t n_poly, void* stream) {
+    return moddown_impl(k, d_acc_q, d_acc_p, d_out, n_poly, nullptr, stream);
+}
+
 // The whole switch: d_c [n_q][N]; d_evk_q [dnum][2][n_q][N]; d_evk_p [dnum][2][n_p][N]; d_out [2][n_q][N].
 // out[0] + out[1] s  ~  c s'   when evk_d = (-a_d s + e_d + P B_d s', a_d) with B_d the CRT basis element of digit d.
-extern "C" int b200fhe_keyswitch_apply(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
-                                       uint64_t* d_out, void* stream) {
+static int apply_impl(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p, uint64_t* d_out,
+                      uint32_t* verdict, void* stream) {
     if (!k || !d_c || !d_evk_q || !d_evk_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: null argument");
     if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
@@ -218,13 +247,40 @@ extern "C" int b200fhe_keyswitch_apply(b200fhe_keyswitch* k, const uint64_t* d_c
     uint64_t* up = k->d_ws + k->o_up;
     uint64_t* accq = k->d_ws + k->o_accq;
     uint64_t* accp = k->d_ws + k->o_accp;
-    RC(b200fhe_keyswitch_modup(k, d_c, up, stream));
+    RC(modup_impl(k, d_c, up, verdict, stream));
     std::vector<const uint64_t*> ct(k->dnum), pt(k->dnum);
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
     RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accq, 2, nq, 0, 0, stream));
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_p + (size_t)d * 2 * np * N; pt[d] = up + ((size_t)d * total + nq) * N; }
     RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accp, 2, np, nq, 0, stream));
-    return b200fhe_keyswitch_moddown(k, accq, accp, d_out, 2, stream);
+    return moddown_impl(k, accq, accp, d_out, 2, verdict ? verdict + (size_t)k->dnum * total : nullptr, stream);
+}
+
+extern "C" int b200fhe_keyswitch_apply(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                                       uint64_t* d_out, void* stream) {
+    return apply_impl(k, d_c, d_evk_q, d_evk_p, d_out, nullptr, stream);
+}
+
+// Same switch with every base conversion checksum-carrying (b200fhe_bconv_modup_protected: scale, memory and contraction
+// checks).  d_verdict [(dnum + 2)][n_q + n_p]: rows 0..dnum-1 = the digits' ModUp conversions (alpha source entries, then
+// the targets in ascending limb order), rows dnum, dnum+1 = the ModDown conversions of out[0], out[1] (n_p source entries,
+// then n_q targets).  All zero = no check failed.  Needs digits and special base of at most 16 limbs.
+extern "C" int b200fhe_keyswitch_apply_protected(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                                                 uint64_t* d_out, uint32_t* d_verdict, void* stream) {
+    if (!d_verdict) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply_protected: null verdict");
+    int rc = apply_impl(k, d_c, d_evk_q, d_evk_p, d_out, d_verdict, stream);
+    if (k) { k->inj_conv = -1; k->inj.clear(); }              // an armed injection is consumed by one call
+    return rc;
+}
+
+// Arms faults for the NEXT b200fhe_keyswitch_apply_protected: `conversion` in [0, dnum) = that digit's ModUp conversion,
+// dnum / dnum + 1 = the ModDown conversion of out[0] / out[1]; entries as in b200fhe_bconv_modup_protected.
+extern "C" int b200fhe_keyswitch_set_inject(b200fhe_keyswitch* k, int conversion, const b200fhe_bconv_inject* inject, size_t n_inject) {
+    if (!k || conversion < 0 || conversion >= k->dnum + 2 || n_inject > B200FHE_BCONV_MAX_INJECT || (n_inject && !inject))
+        return b200_set_err(B200FHE_EINVAL, "keyswitch_set_inject: bad arguments");
+    k->inj_conv = n_inject ? conversion : -1;
+    k->inj.assign(inject, inject + n_inject);
+    return 0;
 }
 
 extern "C" int b200fhe_keyswitch_info(const b200fhe_keyswitch* k, int* n_q, int* n_p, int* dnum, size_t* workspace_bytes) {

@@ -273,6 +273,17 @@ int b200fhe_keyswitch_moddown(b200fhe_keyswitch* plan, const uint64_t* d_acc_q, 
 int b200fhe_keyswitch_apply(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
                             uint64_t* d_out, void* stream);
 
+/* The same switch with every base conversion checksum-carrying (the checks of b200fhe_bconv_modup_protected).
+ * d_verdict [dnum + 2][n_q + n_p] (uint32): rows 0..dnum-1 = the digits' ModUp conversions (alpha source-limb entries, then
+ * the targets in ascending limb order); rows dnum, dnum + 1 = the ModDown conversions of out[0], out[1] (n_p source entries,
+ * then n_q targets).  All zero = every check passed.  Digits and special base of at most 16 limbs. */
+int b200fhe_keyswitch_apply_protected(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                                      uint64_t* d_out, uint32_t* d_verdict, void* stream);
+
+/* Fault injection for the NEXT b200fhe_keyswitch_apply_protected (consumed by it): `conversion` in [0, dnum) = that digit's
+ * ModUp conversion, dnum / dnum + 1 = the ModDown conversion of out[0] / out[1]; entries as in b200fhe_bconv_modup_protected. */
+int b200fhe_keyswitch_set_inject(b200fhe_keyswitch* plan, int conversion, const b200fhe_bconv_inject* inject, size_t n_inject);
+
 /* ---- evaluator steps around the key-switch (NTT-form polynomials [n_poly][L][N]) --------------------
  * The element-wise / permutation kernels phantom::multiply, add_inplace and rotate_inplace run around the
  * key-switch in reliability_test/dotprod_test.cu:113-152. */

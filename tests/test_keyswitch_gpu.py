@@ -120,3 +120,58 @@ def test_bgv_keyswitch_parity_and_plaintext_modulus(pkg, O, log_n, n_q, n_p, dnu
     assert np.array_equal(out, O.keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs, t=t))
     noise = check_switch_noise(O, out, c, s, s_new, moduli[:n_q], tabs[:n_q], bound_bits=44)
     assert not (noise % t).any()
+
+
+@pytest.mark.parametrize("log_n,n_q,n_p,dnum", [(10, 6, 2, 3), (12, 8, 4, 2), (13, 4, 4, 1), (17, 48, 16, 3)])
+def test_protected_keyswitch_same_bits_and_clean_verdict(pkg, O, log_n, n_q, n_p, dnum):
+    """apply_protected (every base conversion checksum-carrying) returns the same bits as apply and an all-zero verdict on
+    a fault-free run; the verdict has one entry per checked limb of each of the dnum + 2 conversions."""
+    import torch
+    N, moduli, ctx, tabs = _setup(pkg, O, log_n, n_q, n_p)
+    ks = pkg.KeySwitch(ctx, n_q, n_p, dnum)
+    g = torch.Generator(device="cuda").manual_seed(log_n)
+    c = torch.randint(0, 1 << 59, (n_q, N), dtype=torch.int64, device="cuda", generator=g)
+    eq = torch.randint(0, 1 << 59, (dnum, 2, n_q, N), dtype=torch.int64, device="cuda", generator=g)
+    ep = torch.randint(0, 1 << 59, (dnum, 2, n_p, N), dtype=torch.int64, device="cuda", generator=g)
+    out = torch.zeros((2, n_q, N), dtype=torch.int64, device="cuda")
+    outp = torch.zeros_like(out)
+    verdict = torch.full((dnum + 2, n_q + n_p), 7, dtype=torch.int32, device="cuda")
+    ks.apply(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), out.data_ptr())
+    for _ in range(2):                                          # twice: the two counter sets alternate
+        ks.apply_protected(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), outp.data_ptr(), verdict.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.equal(out, outp)
+        assert int(verdict.abs().sum().item()) == 0
+
+
+@pytest.mark.parametrize("conversion,inject,row_entry", [
+    (1, [(2, 5, 100, 1 << 17)], lambda nq, np_, a: a + 5),        # digit 1, contraction output of its target #5
+    (0, [(1, 1, 7, 1 << 40)], lambda nq, np_, a: 1),              # digit 0, scale product of source limb 1
+    (3, [(3, 0, 9, 1 << 3)], lambda nq, np_, a: 0),               # ModDown of out[0]: y word flipped in memory
+    (4, [(2, 2, 0, 1)], lambda nq, np_, a: np_ + 2),              # ModDown of out[1]: lowest bit of one output
+])
+def test_protected_keyswitch_flags_the_faulty_conversion(pkg, O, conversion, inject, row_entry):
+    import torch
+    log_n, n_q, n_p, dnum = 11, 6, 2, 3
+    N, moduli, ctx, tabs = _setup(pkg, O, log_n, n_q, n_p)
+    ks = pkg.KeySwitch(ctx, n_q, n_p, dnum)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    c = torch.randint(0, 1 << 59, (n_q, N), dtype=torch.int64, device="cuda", generator=g)
+    eq = torch.randint(0, 1 << 59, (dnum, 2, n_q, N), dtype=torch.int64, device="cuda", generator=g)
+    ep = torch.randint(0, 1 << 59, (dnum, 2, n_p, N), dtype=torch.int64, device="cuda", generator=g)
+    clean = torch.zeros((2, n_q, N), dtype=torch.int64, device="cuda")
+    out = torch.zeros_like(clean)
+    verdict = torch.zeros((dnum + 2, n_q + n_p), dtype=torch.int32, device="cuda")
+    ks.apply(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), clean.data_ptr())
+    ks.set_inject(conversion, inject)
+    ks.apply_protected(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), out.data_ptr(), verdict.data_ptr())
+    torch.cuda.synchronize()
+    v = verdict.cpu().numpy()
+    col = row_entry(n_q, n_p, n_q // dnum)
+    assert v[conversion, col] != 0
+    v[conversion, col] = 0
+    assert not v.any()                                          # only the check of the limb that was hit trips
+    assert not torch.equal(out, clean)                          # ... and the fault did corrupt the result
+    ks.apply_protected(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), out.data_ptr(), verdict.data_ptr())
+    torch.cuda.synchronize()
+    assert int(verdict.abs().sum().item()) == 0 and torch.equal(out, clean)      # the injection was consumed
