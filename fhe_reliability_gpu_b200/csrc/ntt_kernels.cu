@@ -21,6 +21,15 @@ namespace b200 {
 constexpr int kRowLog = 8;          // row length 256
 constexpr int kRowLen = 1 << kRowLog;
 constexpr int kTile = 16;           // columns per column-pass CTA / rows per row-pass CTA
+// Thread groups (of kTile threads) per column-pass CTA.  The two register phases of a column need 2^LB and 2^LA groups.
+// Up to LC = 8 the CTA has max(2^LA, 2^LB) groups (equal there, or the small phase idles a few).  For LC = 9 (radix 32 then
+// radix 16) that left half of the 512 threads idle during the radix-32 phase while their 128 registers kept a second CTA
+// off the SM: the CTA now has min(2^LA, 2^LB) = 16 groups, every thread runs the radix-32 phase and loops twice over the
+// radix-16 phase, and two CTAs fit (N = 2^17: 1.84 -> see profiles/microbench/ntt_size_sweep.py).
+__host__ __device__ constexpr int col_groups(int LC, int LA) {
+    const int LB = LC - LA, hi = LA > LB ? LA : LB, lo = LA > LB ? LB : LA;
+    return 1 << (LC >= 9 ? lo : hi);
+}
 
 
 
@@ -55,9 +64,10 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 // PROT: the protected transform (config C4) -- accumulates the input side of the
 // ABFT checksum while the coefficients are loaded and honours the injection plan.
 template <int LC, int LA, int BIG, bool PROT, bool INJ>
-__global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
+__global__ void __launch_bounds__(kTile * col_groups(LC, LA))
 k_fwd_col(PassArgs p) {
-    constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
+    constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
+    static_assert(NG >= RB, "the first phase runs in one sweep");
     extern __shared__ u64 sm[];
     // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
     // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
@@ -102,17 +112,18 @@ k_fwd_col(PassArgs p) {
     if constexpr (PROT) abft_commit<4>(p.abft, p.limb0 + limb, 0, ck0, ck1);
     if constexpr (LB > 0) {
         __syncthreads();
-        if (g < RA) {
+#pragma unroll 1
+        for (int gb = g; gb < RA; gb += NG) {
             u64 w[RB];
 #pragma unroll
-            for (int e = 0; e < RB; e++) w[e] = sm[(g * RB + e) * kTile + c];
+            for (int e = 0; e < RB; e++) w[e] = sm[(gb * RB + e) * kTile + c];
             if constexpr (INJ)
-                ct_phase<LB, BIG>(w, TwShared{stw, (1u << LA) + g}, m,
-                                  Inject{p.inj, p.n_inj, p.limb0 + limb, (u32)(g * RB) * kRowLen + col, (u32)kRowLog, (u32)LA, m.q});
+                ct_phase<LB, BIG>(w, TwShared{stw, (1u << LA) + gb}, m,
+                                  Inject{p.inj, p.n_inj, p.limb0 + limb, (u32)(gb * RB) * kRowLen + col, (u32)kRowLog, (u32)LA, m.q});
             else
-                ct_phase<LB, BIG>(w, TwShared{stw, (1u << LA) + g}, m);
+                ct_phase<LB, BIG>(w, TwShared{stw, (1u << LA) + gb}, m);
 #pragma unroll
-            for (int e = 0; e < RB; e++) base[(size_t)(g * RB + e) * kRowLen + c] = w[e];
+            for (int e = 0; e < RB; e++) base[(size_t)(gb * RB + e) * kRowLen + c] = w[e];
         }
     }
 }
@@ -268,9 +279,10 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs
 
 // ---------------------------------------------------------------- inverse, columns
 template <int LC, int LA, int BIG>
-__global__ void __launch_bounds__(kTile << ((LA > LC - LA) ? LA : LC - LA))
+__global__ void __launch_bounds__(kTile * col_groups(LC, LA))
 k_inv_col(PassArgs p) {
-    constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB;
+    constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
+    static_assert(NG >= RB, "the last phase runs in one sweep");
     extern __shared__ u64 sm[];
     // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
     // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
@@ -284,16 +296,29 @@ k_inv_col(PassArgs p) {
     for (int i = threadIdx.x; i < (1 << LC); i += blockDim.x) stw[i] = __ldg(itw + i);
     if constexpr (LB == 0) __syncthreads();
     if constexpr (LB > 0) {
-        u64 w[RB];
-        if (g < RA) {
+        if constexpr (NG >= RA) {
+            u64 w[RB];
+            if (g < RA) {
 #pragma unroll
-            for (int e = 0; e < RB; e++) w[e] = base[(size_t)(g * RB + e) * kRowLen + c];
-        }
-        __syncthreads();
-        if (g < RA) {
-            gs_phase<LB, BIG, false>(w, TwShared{stw, (1u << LA) + g}, m);
+                for (int e = 0; e < RB; e++) w[e] = base[(size_t)(g * RB + e) * kRowLen + c];
+            }
+            __syncthreads();
+            if (g < RA) {
+                gs_phase<LB, BIG, false>(w, TwShared{stw, (1u << LA) + g}, m);
 #pragma unroll
-            for (int e = 0; e < RB; e++) sm[(g * RB + e) * kTile + c] = w[e];
+                for (int e = 0; e < RB; e++) sm[(g * RB + e) * kTile + c] = w[e];
+            }
+        } else {
+            __syncthreads();                                   // twiddles staged
+#pragma unroll 1
+            for (int gb = g; gb < RA; gb += NG) {
+                u64 w[RB];
+#pragma unroll
+                for (int e = 0; e < RB; e++) w[e] = base[(size_t)(gb * RB + e) * kRowLen + c];
+                gs_phase<LB, BIG, false>(w, TwShared{stw, (1u << LA) + gb}, m);
+#pragma unroll
+                for (int e = 0; e < RB; e++) sm[(gb * RB + e) * kTile + c] = w[e];
+            }
         }
         __syncthreads();
     }
@@ -404,7 +429,7 @@ static void launch_fwd2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_
     dim3 gc((kRowLen / kTile) * np, a.L), gr(((a.N >> kRowLog) / kRowsPerCta) * np, a.L);
     constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (mask & 1) k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
+    if (mask & 1) k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
     if (mask & 2) {
         cudaFuncSetAttribute(k_fwd_row<BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
         k_fwd_row<BIG, PROT, INJ><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
@@ -423,7 +448,7 @@ static void launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_
     }
     constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_inv_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (mask & 2) k_inv_col<LC, LA, BIG><<<gc, kTile << (LA > LB ? LA : LB), smem, s>>>(a);
+    if (mask & 2) k_inv_col<LC, LA, BIG><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
 }
 
 template <int BIG>
