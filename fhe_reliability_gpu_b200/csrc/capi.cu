@@ -273,7 +273,7 @@ static size_t chunk_polys(const b200fhe_ctx* c, size_t L) {
     return n ? n : 1;
 }
 static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, size_t L, size_t start, int mask,
-                   cudaStream_t s) {
+                   cudaStream_t s, const B200Mod* mods_alt = nullptr) {
     if (!c || (!d && n_poly && L)) return b200_set_err(B200FHE_EINVAL, "nwt: null argument");
     if (L == 0 || n_poly == 0) return 0;
     if (start + L > (size_t)c->L) return b200_set_err(B200FHE_EINVAL, "nwt: start_mod %zu + L %zu exceeds context (%d)", start, L, c->L);
@@ -288,7 +288,7 @@ static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, siz
     const int big = (all_near && !no_near) ? 2 : all_big ? 1 : 0;
     CK(cudaSetDevice(c->device));
     PassArgs a;
-    a.mods = c->d_mods;
+    a.mods = mods_alt ? mods_alt : c->d_mods;
     a.tw = inverse ? c->d_itw : c->d_tw;
     a.rtw = inverse ? c->d_irtw : c->d_rtw;
     a.N = (u32)c->N;
@@ -311,6 +311,12 @@ extern "C" int b200fhe_nwt_forward(b200fhe_ctx* c, uint64_t* d, size_t n_poly, s
 }
 extern "C" int b200fhe_nwt_backward(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, void* stream) {
     return run_ntt(c, true, d, n_poly, L, start, 3, (cudaStream_t)stream);
+}
+// Inverse transform whose final N^-1 scaling uses an alternative per-modulus constant table (same layout as the context's
+// B200Mod array, ninv / iw1n replaced by ninv c_l / iw1n c_l): the key-switch folds the base conversion's scale step
+// y_j = x_j (D/q_j)^-1 into the inverse NTT this way (keyswitch.cu).
+int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream) {
+    return run_ntt(c, true, d, n_poly, L, start, 3, (cudaStream_t)stream, d_mods_alt);
 }
 // measurement hook: one pass (1 = first kernel, 2 = second kernel) of the transform
 extern "C" int b200fhe_debug_nwt_pass(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, int inverse,

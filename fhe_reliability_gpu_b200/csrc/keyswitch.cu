@@ -3,9 +3,10 @@
 // NTT 48 % + base conversion 42 % of it at dnum = 3, profile_framewk/draw_dnum.py:5-9):
 //
 //   c  [n_q][N]  (NTT domain, moduli q_0..q_{n_q-1})
-//   1. x = INTT(c)                                       one batched launch over all digits
-//   2. per digit d (limbs [d a, (d+1) a)):  y_d = x_d (D_d/q_j)^-1 mod q_j            (k_bconv_scale)
-//      up_d[targets] = NTT( sum_j y_dj (D_d/q_j) mod target )                          (k_bconv_contract + NTT)
+//   1. y = INTT(c) (D_d/q_j)^-1 mod q_j                  one batched launch over all digits; the conversion's scale step is
+//                                                        folded into the transform's final N^-1 constant (d_mods_scaled)
+//   2. per digit d (limbs [d a, (d+1) a)):
+//      up_d[targets] = NTT( sum_j y_dj (D_d/q_j) mod target )                          (k_bconv_contract_tc + NTT)
 //      up_d[digit limbs] = c[digit limbs]                                              (pass through)
 //   3. acc[p] = sum_d up_d (.) evk_d[p],  p = 0,1, over all n_q + n_p limbs             (k_pmult, T = dnum)
 //   4. ModDown: t = INTT(acc[p] mod P);  conv = NTT( BaseConv_{P->Q}(t) );
@@ -25,6 +26,7 @@ using namespace b200;
 
 int b200_set_err(int code, const char* fmt, ...);
 void b200_count_launches(unsigned n);
+int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream);
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -45,6 +47,7 @@ struct b200fhe_keyswitch {
     std::vector<b200fhe_bconv*> up;      // per digit: digit limbs -> every other limb of Q u P
     b200fhe_bconv* down = nullptr;       // P -> Q
     ulonglong2* d_pinv = nullptr;        // [n_q] (P^-1 mod q_l, Shoup quotient)
+    B200Mod* d_mods_scaled = nullptr;    // [n_q + n_p] the context's constants with N^-1 replaced by N^-1 * (conversion scale of the limb)
     uint64_t* d_ws = nullptr;                 // workspace, see offsets
     size_t o_x = 0, o_y = 0, o_up = 0, o_accq = 0, o_accp = 0, o_conv = 0, ws_words = 0;
     // fault injection armed for the next protected apply (b200fhe_keyswitch_set_inject)
@@ -82,6 +85,7 @@ extern "C" int b200fhe_keyswitch_destroy(b200fhe_keyswitch* k) {
     for (b200fhe_bconv* p : k->up) b200fhe_bconv_destroy(p);
     b200fhe_bconv_destroy(k->down);
     if (k->d_pinv) cudaFree(k->d_pinv);
+    if (k->d_mods_scaled) cudaFree(k->d_mods_scaled);
     if (k->d_ws) cudaFree(k->d_ws);
     delete k;
     return 0;
@@ -133,6 +137,28 @@ extern "C" int b200fhe_keyswitch_create_bgv(b200fhe_ctx* c, int n_q, int n_p, in
         const uint64_t iv = nt::invmod(P, q);
         pinv[l] = make_ulonglong2(iv, nt::shoup(iv, q));
     }
+    // scale step of every conversion folded into the inverse NTT that precedes it: limb l of Q belongs to exactly one digit,
+    // the limbs of P to the ModDown conversion
+    std::vector<B200Mod> ms(c->h_mods.begin(), c->h_mods.begin() + total);
+    for (int l = 0; l < total; l++) {
+        const uint64_t q = c->moduli[l];
+        int lo, hi;                                                   // the source base this limb is converted from
+        uint64_t extra = 1;
+        if (l < n_q) {
+            if (!dnum) continue;
+            lo = (l / alpha) * alpha; hi = lo + alpha;
+        } else {
+            lo = n_q; hi = total; extra = plain_modulus % q;
+        }
+        uint64_t h = extra;
+        for (int i = lo; i < hi; i++)
+            if (i != l) h = nt::mulmod(h, c->moduli[i] % q, q);
+        const uint64_t iv = nt::invmod(h, q);
+        ms[l].ninv = nt::mulmod(ms[l].ninv, iv, q);
+        ms[l].ninv_s = nt::shoup(ms[l].ninv, q);
+        ms[l].iw1n = nt::mulmod(ms[l].iw1n, iv, q);
+        ms[l].iw1n_s = nt::shoup(ms[l].iw1n, q);
+    }
     const size_t N = c->N;
     size_t o = 0;
     k->o_x = o;    o += dnum ? (size_t)n_q * N : 0;                                  // INTT(c)
@@ -145,6 +171,8 @@ extern "C" int b200fhe_keyswitch_create_bgv(b200fhe_ctx* c, int n_q, int n_p, in
     cudaError_t e = cudaSetDevice(c->device);
     if (e == cudaSuccess) e = cudaMalloc(&k->d_pinv, sizeof(ulonglong2) * n_q);
     if (e == cudaSuccess) e = cudaMalloc(&k->d_ws, sizeof(uint64_t) * o);
+    if (e == cudaSuccess) e = cudaMalloc(&k->d_mods_scaled, sizeof(B200Mod) * total);
+    if (e == cudaSuccess) e = cudaMemcpy(k->d_mods_scaled, ms.data(), sizeof(B200Mod) * total, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(k->d_pinv, pinv.data(), sizeof(ulonglong2) * n_q, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
         b200fhe_keyswitch_destroy(k);
@@ -174,7 +202,10 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
     for (int d = 0; d < k->dnum; d++)
         CK(cudaMemcpyAsync(d_up + ((size_t)d * total + (size_t)d * a) * N, d_c + (size_t)d * a * N, sizeof(uint64_t) * a * N,
                            cudaMemcpyDeviceToDevice, s));
-    RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
+    // unprotected: the inverse NTT's final constant carries the conversion's scale step, so x already IS y = x (D/q_j)^-1;
+    // protected: plain inverse NTT, the scale step runs as its own checked kernel
+    if (verdict) RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
+    else RC(b200_nwt_backward_mods(c, x, 1, (size_t)k->n_q, 0, k->d_mods_scaled, stream));
     for (int d = 0; d < k->dnum; d++) {
         b200fhe_bconv* p = k->up[d];
         const uint64_t* xd = x + (size_t)d * a * N;
@@ -186,9 +217,8 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
             RC(b200_bconv_modup_protected_split(p, xd, yd, upd, upd + (below + a) * N, below, verdict + (size_t)d * total, nullptr,
                                                 hit ? k->inj.data() : nullptr, hit ? k->inj.size() : 0, stream));
         } else {
-            RC(b200fhe_bconv_scale(p, xd, yd, 0, a, stream));
-            RC(b200fhe_bconv_contract(p, yd, upd, 0, below, stream));
-            RC(b200fhe_bconv_contract(p, yd, upd + (below + a) * N, below, above, stream));
+            RC(b200fhe_bconv_contract(p, xd, upd, 0, below, stream));
+            RC(b200fhe_bconv_contract(p, xd, upd + (below + a) * N, below, above, stream));
         }
         if (below) RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
         RC(b200fhe_nwt_forward(c, upd + (below + a) * N, 1, above, below + a, stream));
@@ -212,15 +242,15 @@ static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t*
     const size_t N = c->N, nq = (size_t)k->n_q, np = (size_t)k->n_p;
     uint64_t* y = k->d_ws + k->o_y;
     uint64_t* conv = k->d_ws + k->o_conv;
-    RC(b200fhe_nwt_backward(c, d_acc_p, n_poly, np, nq, stream));
+    if (verdict) RC(b200fhe_nwt_backward(c, d_acc_p, n_poly, np, nq, stream));
+    else RC(b200_nwt_backward_mods(c, d_acc_p, n_poly, np, nq, k->d_mods_scaled, stream));     // scale step folded in: acc_p is y
     for (size_t p = 0; p < n_poly; p++) {
         if (verdict) {
             const bool hit = k->inj_conv == k->dnum + (int)p;
             RC(b200_bconv_modup_protected_split(k->down, d_acc_p + p * np * N, y + p * np * N, conv + p * nq * N, nullptr, 0,
                                                 verdict + p * (np + nq), nullptr, hit ? k->inj.data() : nullptr, hit ? k->inj.size() : 0, stream));
         } else {
-            RC(b200fhe_bconv_scale(k->down, d_acc_p + p * np * N, y + p * np * N, 0, np, stream));
-            RC(b200fhe_bconv_contract(k->down, y + p * np * N, conv + p * nq * N, 0, nq, stream));
+            RC(b200fhe_bconv_contract(k->down, d_acc_p + p * np * N, conv + p * nq * N, 0, nq, stream));
         }
     }
     RC(b200fhe_nwt_forward(c, conv, n_poly, nq, 0, stream));
