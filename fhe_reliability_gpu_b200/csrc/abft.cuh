@@ -41,6 +41,10 @@ struct AbftOut {
         u32 o0, o1;
         unpack64(om, o0, o1);
         const u32 x0 = (u32)x & 0x3fffffffu, x1 = (u32)(x >> 30);
+#ifdef B200_ABL_ABFT_NOOUTMUL        // timing ablation: weights still loaded and consumed, no multiplier-pipe work
+        p00 += (u64)(o0 ^ x0); p01 += (u64)(o1 ^ x1);
+        return;
+#endif
         asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p00) : "r"(o0), "r"(x0));
         asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p01) : "r"(o0), "r"(x1));
         asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(p10) : "r"(o1), "r"(x0));
@@ -65,6 +69,9 @@ template <int NDIG>
 __device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u64 s0, u64 s1) {
     u64* c = counters + ((size_t)limb * 2 + side) * kAbftStride;
     constexpr u32 mask = (1u << kAbftDigit) - 1u;
+#ifdef B200_ABL_ABFT_NOCOMMIT        // timing ablation (profiles/microbench/runexp.sh): sums stay live, no REDUX / RED
+    if ((s0 ^ s1) != 0x9E3779B97F4A7C15ull) return;
+#endif
 #pragma unroll
     for (int d = 0; d < NDIG; d++) {
         const int sh = kAbftDigit * d;
