@@ -14,8 +14,8 @@
 // 64-bit sums; omega_k and the canonical outputs are split at 30 bits so the four
 // partial products of 16 coefficients fit 64-bit sums.  One Barrett reduction
 // partial products of 16 coefficients fit 64-bit sums.  The per-thread sums are committed
-// unreduced (26-bit digits, one REDUX + one RED per digit per warp); the single modular
-// reduction per limb happens in k_abft_finalize.
+// unreduced (26-bit digits, one REDUX per digit per warp, the warps' digit sums added in shared memory,
+// one RED per digit per CTA); the single modular reduction per limb happens in k_abft_finalize.
 #pragma once
 #include "modarith.cuh"
 
@@ -61,14 +61,18 @@ struct AbftOut {
 };
 
 // counters: [limb][side][8] u64, side 0 = input sum, 1 = output sum.  The 128-bit per-thread sum
-// (s1:s0) is committed unreduced as NDIG 26-bit digits: one REDUX per digit and one atomic per digit
-// per warp; k_abft_finalize recombines the digit sums and reduces mod q once per limb.
+// (s1:s0) is committed unreduced as NDIG 26-bit digits: one REDUX per digit per warp and one atomic per
+// digit per CTA (-DB200_ABFT_WARP_COMMIT: per warp, the r1c form; 17.9 % -> 16.6 % overhead at C2's shape);
+// k_abft_finalize recombines the digit sums and reduces mod q once per limb.  CTA-uniform call sites only.
 constexpr int kAbftStride = 8;
 constexpr int kAbftDigit = 26;       // 32 lanes x 26-bit digits sum to < 2^31: one 32-bit REDUX per digit
 template <int NDIG>
 __device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u64 s0, u64 s1) {
     u64* c = counters + ((size_t)limb * 2 + side) * kAbftStride;
     constexpr u32 mask = (1u << kAbftDigit) - 1u;
+#ifndef B200_ABFT_WARP_COMMIT
+    __shared__ u32 red[32][NDIG];        // per-warp digit sums (< 2^31 each); every thread of the CTA calls this
+#endif
 #ifdef B200_ABL_ABFT_NOCOMMIT        // timing ablation (profiles/microbench/runexp.sh): sums stay live, no REDUX / RED
     if ((s0 ^ s1) != 0x9E3779B97F4A7C15ull) return;
 #endif
@@ -79,10 +83,23 @@ __device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u
         if (sh + kAbftDigit <= 64) dig = (u32)(s0 >> sh) & mask;
         else if (sh >= 64) dig = (u32)(s1 >> (sh - 64)) & mask;
         else dig = (u32)((s0 >> sh) | (s1 << (64 - sh))) & mask;
-        const u64 sum = __reduce_add_sync(0xffffffffu, dig);
+        const u32 sum = __reduce_add_sync(0xffffffffu, dig);
+#ifndef B200_ABFT_WARP_COMMIT
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][d] = sum;
+#else
         // plain RED from lane 0 (inline PTX: atomicAdd here makes nvcc emit its warp-aggregation sequence per digit)
-        if ((threadIdx.x & 31) == 0) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(c + d), "l"(sum) : "memory");
+        if ((threadIdx.x & 31) == 0) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(c + d), "l"((u64)sum) : "memory");
+#endif
     }
+#ifndef B200_ABFT_WARP_COMMIT
+    // one RED per digit per CTA instead of per warp: the counters of a limb are one hot L2 line
+    __syncthreads();
+    if (threadIdx.x < NDIG) {
+        u64 tot = 0;
+        for (u32 w = 0; w < (blockDim.x + 31) / 32; w++) tot += red[w][threadIdx.x];
+        asm volatile("red.global.add.u64 [%0], %1;" ::"l"(c + threadIdx.x), "l"(tot) : "memory");
+    }
+#endif
 }
 
 // generate_weights(N): w_i = (i mod p) + (i div p) + 2, p = 2^pl

@@ -93,7 +93,11 @@ k_fwd_col(PassArgs p) {
             AbftIn acc;
             const int pl = (LC + kRowLog + 1) / 2;
 #pragma unroll
+#ifdef B200_ABL_ABFT_NOIN            // timing ablation: no weighted products on the input side
+            for (int e = 0; e < RA; e++) acc.lo ^= v[e];
+#else
             for (int e = 0; e < RA; e++) acc.add(abft_w((u32)(e * RB + g) * kRowLen + col, pl), v[e]);
+#endif
             acc.value(ck0, ck1);
         }
         if constexpr (INJ)
@@ -202,7 +206,11 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
         const u32 a0 = cl * 128 + ((cl & 7) << 4);
         const unsigned char* om = reinterpret_cast<const unsigned char*>(p.omega + (size_t)mi * p.N + x0 + cl * 16);
 #pragma unroll
+#ifndef B200_ABL_ABFT_NOOMEGA        // timing ablation: the weights are whatever the exchange tile holds
         for (int c = 0; c < 8; c++)
+#else
+        for (int c = 0; c < 0; c++)
+#endif
             asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(xrow + (a0 ^ (c << 4)))), "l"(om + c * 16) : "memory");
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
