@@ -39,6 +39,8 @@ SIGNATURES = {
     "b200fhe_nwt_forward_protected_host": (i32, [vp, U64P, sz, sz, sz, C.POINTER(C.c_uint32), U64P, vp, sz]),
     "b200fhe_abft_weights": (i32, [vp, i32, U64P, U64P]),
     "b200fhe_four_step_protected_host": (i32, [u64, u64, sz, U64P, U64P, sz, U64P, C.POINTER(C.c_uint32), vp, sz, i32]),
+    "b200fhe_relia_op_ranges": (i32, [sz, U64P, U64P, U64P]),
+    "b200fhe_relia_four_step_host": (i32, [u64, u64, sz, i32, U64P, U64P, U64P, sz, vp, sz, C.POINTER(C.c_uint32), i32]),
     "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_bconv_create": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, C.POINTER(vp)]),
@@ -375,3 +377,39 @@ def four_step_protected_host(a, mod, g, plan=(), device=0):
     check(lib().b200fhe_four_step_protected_host(mod, g, N, _p(a), _p(y), batch, _p(checks),
                                                  verdict.ctypes.data_as(C.POINTER(C.c_uint32)), C.cast(arr, vp), len(plan), device))
     return y, checks, verdict
+
+
+class ReliaFault(C.Structure):
+    """b200fhe_relia_fault: one corrupted operation of one trial (relia_ntt_sim.cpp's running op index)."""
+    _fields_ = [("trial", C.c_uint32), ("kind", C.c_uint32), ("op", C.c_uint64), ("payload", C.c_uint64)]
+
+
+def relia_op_ranges(N):
+    """(s1_end, s2_end, s3_end): the simulator's OpRanges for N = n1 n2."""
+    a, b, c = u64(), u64(), u64()
+    check(lib().b200fhe_relia_op_ranges(N, C.byref(a), C.byref(b), C.byref(c)))
+    return int(a.value), int(b.value), int(c.value)
+
+
+def relia_four_step_host(q, g, a, weights, faults=(), fold_bits=4, want_out=True, device=0):
+    """four_step_ntt of relia_ntt_sim.cpp for a [trials][N]; weights [trials][2 n2 + n1]; faults: iterable of
+    (trial, op, kind, payload) or a ready (ReliaFault * n) array.  Returns (out or None, flags [trials] uint32)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    weights = np.ascontiguousarray(weights, dtype=np.uint64)
+    trials, N = a.shape
+    if isinstance(faults, np.ndarray):          # structured array with b200fhe_relia_fault's layout (24-byte records)
+        assert faults.dtype.itemsize == C.sizeof(ReliaFault) and faults.flags.c_contiguous
+        arr, nf = faults.ctypes.data_as(vp), len(faults)
+    elif isinstance(faults, C.Array):
+        arr, nf = faults, len(faults)
+    else:
+        faults = list(faults)
+        nf = len(faults)
+        arr = (ReliaFault * max(nf, 1))()
+        for i, (tr, op, kind, payload) in enumerate(faults):
+            arr[i] = ReliaFault(int(tr), int(kind), int(op), int(payload))
+    out = np.zeros_like(a) if want_out else None
+    flags = np.zeros(trials, dtype=np.uint32)
+    check(lib().b200fhe_relia_four_step_host(q, g, N, fold_bits, _p(a), _p(out) if want_out else None, _p(weights), trials,
+                                             C.cast(arr, vp), nf, flags.ctypes.data_as(C.POINTER(C.c_uint32)), device))
+    return out, flags

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <atomic>
 
 using namespace b200;
 
@@ -253,8 +254,8 @@ extern "C" int b200fhe_ctx_moduli(const b200fhe_ctx* c, uint64_t* out) {
 }
 
 // ---------------------------------------------------------------- transforms
-static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py's gpu_launches)
-extern "C" unsigned long long b200fhe_launch_count(void) { return g_launches; }
+static std::atomic<unsigned long long> g_launches{0};   // kernels launched by this library (bench.py's gpu_launches)
+extern "C" unsigned long long b200fhe_launch_count(void) { return g_launches.load(); }
 void b200_count_launches(unsigned n) { g_launches += n; }
 
 // Polynomials per launch on the device-resident path.  The transform is bound by the integer
@@ -427,24 +428,35 @@ extern "C" int b200fhe_nwt_backward_host(b200fhe_ctx* c, uint64_t* h, size_t n_p
 
 // ---------------------------------------------------------------- protected forward NTT
 static int check_limbs(const b200fhe_ctx* c, size_t L, size_t start, const char* what);
-static int ensure_abft(b200fhe_ctx* c, size_t start, size_t L, size_t n_limbs) {
+// Counters and injection staging are rings of kAbftSlots slices, one per protected call: calls on different streams do
+// not share a counter set (up to kAbftSlots in flight).  Everything is ordered on the CALLER's stream s: the counters of a
+// new (or regrown) allocation are cleared with cudaMemsetAsync(s), the output weights are uploaded with
+// cudaMemcpyAsync(s) + a synchronise (pageable source), so the first abft_commit RED cannot race either of them.
+static int ensure_abft(b200fhe_ctx* c, size_t start, size_t L, size_t n_limbs, cudaStream_t s) {
     if (!c->d_omega) CK(cudaMalloc(&c->d_omega, sizeof(uint64_t) * c->N * c->L));
-    if (!c->d_inj) CK(cudaMalloc(&c->d_inj, sizeof(InjEntry) * B200FHE_MAX_INJECT));
+    if (!c->d_inj) CK(cudaMalloc(&c->d_inj, sizeof(InjEntry) * B200FHE_MAX_INJECT * kAbftSlots));
     if (c->abft_limbs < n_limbs) {
-        if (c->d_abft) cudaFree(c->d_abft);
+        if (c->d_abft) { CK(cudaDeviceSynchronize()); cudaFree(c->d_abft); }     // earlier calls may still use the old ring
         c->d_abft = nullptr; c->abft_limbs = 0;
-        CK(cudaMalloc(&c->d_abft, sizeof(uint64_t) * 16 * n_limbs));
-        CK(cudaMemset(c->d_abft, 0, sizeof(uint64_t) * 16 * n_limbs));
+        CK(cudaMalloc(&c->d_abft, sizeof(uint64_t) * 16 * n_limbs * kAbftSlots));
+        CK(cudaMemsetAsync(c->d_abft, 0, sizeof(uint64_t) * 16 * n_limbs * kAbftSlots, s));
+        CK(cudaStreamSynchronize(s));           // other streams may take the next slots
         c->abft_limbs = n_limbs;
+        c->abft_dirty = 0;
     }
-    std::vector<uint64_t> om(c->N);
+    std::vector<uint64_t> om;
+    bool uploaded = false;
     for (size_t i = start; i < start + L; i++) {
         if (c->has_omega[i]) continue;
+        om.resize(c->N);
         nt::abft_output_weights(c->log_n, c->moduli[i], c->psi[i], om.data());
         for (size_t k = 0; k < c->N; k++) om[k] = (om[k] & 0x3fffffffull) | ((om[k] >> 30) << 32);   // 30-bit halves
-        CK(cudaMemcpy(c->d_omega + i * c->N, om.data(), sizeof(uint64_t) * c->N, cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(c->d_omega + i * c->N, om.data(), sizeof(uint64_t) * c->N, cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));           // om is reused for the next modulus
         c->has_omega[i] = 1;
+        uploaded = true;
     }
+    if (uploaded) CK(cudaDeviceSynchronize());  // the table is shared by every stream
     return 0;
 }
 
@@ -464,9 +476,17 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
     if (n_plan > B200FHE_MAX_INJECT || (n_plan && !plan)) return b200_set_err(B200FHE_EINVAL, "nwt_protected: bad injection plan");
     const size_t n_limbs = n_poly * L;
     CK(cudaSetDevice(c->device));
-    rc = ensure_abft(c, start, L, n_limbs);
-    if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
+    rc = ensure_abft(c, start, L, n_limbs, s);
+    if (rc) return rc;
+    // this call's slice of the rings
+    const unsigned slot = c->abft_next++ % kAbftSlots;
+    u64* d_cnt = (u64*)c->d_abft + (size_t)slot * 16 * c->abft_limbs;
+    InjEntry* d_inj = c->d_inj + (size_t)slot * B200FHE_MAX_INJECT;
+    if (c->abft_dirty & (1u << slot)) {         // a call on this slot failed midway: its counters may be non-zero
+        CK(cudaMemsetAsync(d_cnt, 0, sizeof(uint64_t) * 16 * n_limbs, s));
+        c->abft_dirty &= ~(1u << slot);
+    }
     InjEntry h[B200FHE_MAX_INJECT];
     for (size_t i = 0; i < n_plan; i++) {
         if (plan[i].limb >= n_limbs || plan[i].stage >= (uint32_t)c->log_n || plan[i].butterfly >= c->N / 2 || plan[i].kind < 1 || plan[i].kind > 2)
@@ -478,7 +498,11 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
         h[i].kind = plan[i].kind;
         h[i].payload = plan[i].payload;
     }
-    if (n_plan) CK(cudaMemcpyAsync(c->d_inj, h, sizeof(InjEntry) * n_plan, cudaMemcpyHostToDevice, s));
+    if (n_plan) {
+        CK(cudaMemcpyAsync(d_inj, h, sizeof(InjEntry) * n_plan, cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));           // h[] is a stack buffer
+    }
+    c->abft_dirty |= (1u << slot);              // cleared once finalize (which zeroes the counters) is enqueued
     bool all_big = true, all_near = true;
     for (size_t i = start; i < start + L; i++) {
         all_big = all_big && c->h_mods[i].big;
@@ -493,8 +517,8 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
     a.L = (u32)L;
     a.start_mod = (u32)start;
     a.omega = (const u64*)c->d_omega;
-    a.abft = (u64*)c->d_abft;
-    a.inj = c->d_inj;
+    a.abft = d_cnt;
+    a.inj = d_inj;
     a.n_inj = (u32)n_plan;
     size_t step = chunk_polys(c, L);
     if (step * L > 32768) step = 32768 / L ? 32768 / L : 1;
@@ -506,10 +530,10 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
         if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt_protected: log_n=%d unsupported (rc=%d)", c->log_n, rc);
         g_launches += c->log_n <= 11 ? 1 : 2;
     }
-    launch_abft_finalize((u64*)c->d_abft, c->d_mods, (u32)L, (u32)start, (u32)n_limbs, d_verdict, (u64*)d_sums, s);
+    launch_abft_finalize(d_cnt, c->d_mods, (u32)L, (u32)start, (u32)n_limbs, d_verdict, (u64*)d_sums, s);
     g_launches += 1;
     CK(cudaGetLastError());
-    if (n_plan) CK(cudaStreamSynchronize(s));   // h[] is a stack buffer
+    c->abft_dirty &= ~(1u << slot);
     return 0;
 }
 
@@ -556,8 +580,10 @@ extern "C" int b200fhe_pmult_accum(b200fhe_ctx* c, const uint64_t* const* ct, co
     for (size_t k = 0; k < T; k++)
         if (!ct[k] || !pt[k]) return b200_set_err(B200FHE_EINVAL, "pmult: null term %zu", k);
     CK(cudaSetDevice(c->device));
+    unsigned long long nl_ = 0;
     rc = launch_pmult((const u64* const*)ct, (const u64* const*)pt, T, (u64*)d_out, c->d_mods, (u32)c->N, (u32)P, (u32)L, (u32)start,
-                      accumulate, (cudaStream_t)stream, &g_launches);
+                      accumulate, (cudaStream_t)stream, &nl_);
+    g_launches += nl_;
     if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "pmult: N=%zu unsupported", c->N);
     CK(cudaGetLastError());
     return 0;
@@ -790,9 +816,11 @@ int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uin
     u64* nxt = p->d_cnt + (size_t)(p->cnt_set ^ 1) * n_cnt;
     p->cnt_set ^= 1;
     static_assert(sizeof(b200fhe_bconv_inject) == 24, "layout shared with BconvInj");
+    unsigned long long nl2_ = 0;
     int rc = launch_bconv_modup_protected((const u64*)d_in, (u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_src, p->d_dst, p->d_inv, p->d_hat, p->d_btab,
                                           (u32)p->ctx->N, (u32)p->m, (u32)p->K, cur, nxt, d_verdict, (u64*)d_sums, inject, (u32)n_inject,
-                                          (cudaStream_t)stream, &g_launches, (u64*)d_out_hi, (u32)k_split);
+                                          (cudaStream_t)stream, &nl2_, (u64*)d_out_hi, (u32)k_split);
+    g_launches += nl2_;
     if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup_protected: unsupported plan");
     CK(cudaGetLastError());
     return 0;

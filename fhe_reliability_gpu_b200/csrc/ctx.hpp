@@ -65,6 +65,8 @@ int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* 
 
 }  // namespace b200
 
+constexpr unsigned kAbftSlots = 4;   // protected calls that may be in flight per context (each has its own counters)
+
 struct b200fhe_ctx {
     int log_n = 0;
     size_t N = 0;
@@ -82,9 +84,11 @@ struct b200fhe_ctx {
     // ABFT (built lazily by the first protected call)
     uint64_t* d_omega = nullptr;     // [L][N]
     std::vector<uint8_t> has_omega;  // per modulus
-    uint64_t* d_abft = nullptr;      // counters, grown on demand
+    uint64_t* d_abft = nullptr;      // counters: ring of kAbftSlots slices of 16 abft_limbs words, grown on demand
     size_t abft_limbs = 0;
-    InjEntry* d_inj = nullptr;       // injection plan staging (kMaxInject entries)
+    unsigned abft_next = 0;          // next ring slot (one per protected call)
+    unsigned abft_dirty = 0;         // bit s: slot s may hold non-zero counters (a call failed between launch and finalize)
+    InjEntry* d_inj = nullptr;       // injection plan staging, kAbftSlots x B200FHE_MAX_INJECT entries
     // host-buffer entry points: pinned staging + device scratch, grown on demand
     uint64_t* h_stage = nullptr;
     uint64_t* d_stage = nullptr;

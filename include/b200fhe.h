@@ -14,6 +14,10 @@
  * start_mod + l of the context (Phantom's `start_modulus_idx`).
  * There is no CPU fallback: a call without a usable CUDA device fails with
  * B200FHE_ECUDA.
+ * Threading: b200fhe_last_error() is thread-local; a context and the plans made from it
+ * carry scratch buffers (staging, workspaces, counters), so calls on ONE context or plan
+ * must come from one host thread at a time and, unless an entry point says otherwise, be
+ * serialised on one stream.  Use one context per host thread / per rank.
  */
 #ifndef B200FHE_H
 #define B200FHE_H
@@ -135,8 +139,10 @@ typedef struct b200fhe_inject {
  * reliability_test/four_step_ntt_prot.py:185-252 and evaluated in relia_ntt_sim.cpp.
  * d_verdict[n_poly*L] receives 0 (checksums agree) or 1 (fault detected); d_sums
  * (optional, [n_poly*L][2]) receives the input- and output-side checksum.  h_plan /
- * n_plan (optional, host memory, <= B200FHE_MAX_INJECT) inject faults.  One
- * protected call may be in flight per context. */
+ * n_plan (optional, host memory, <= B200FHE_MAX_INJECT) inject faults.  Each call takes
+ * its own slice of the context's checksum counters: up to 4 protected calls may be in
+ * flight per context (on different streams); all work, including the first-use upload of
+ * the weights, is ordered on `stream`. */
 int b200fhe_nwt_forward_protected(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_poly, size_t L, size_t start_mod,
                                   uint32_t* d_verdict, uint64_t* d_sums, const b200fhe_inject* h_plan, size_t n_plan,
                                   void* stream);
@@ -170,6 +176,33 @@ typedef struct b200fhe_fs_inject {
 int b200fhe_four_step_protected_host(uint64_t mod, uint64_t g, size_t N, const uint64_t* h_in, uint64_t* h_out, size_t batch,
                                      uint64_t* h_checks, uint32_t* h_verdict, const b200fhe_fs_inject* plan, size_t n_plan,
                                      int device);
+
+/* ---- the protected four-step NTT the reference evaluated (rfhe_framewk/src/ntt_test/relia_ntt_sim.cpp) ---- */
+
+/* One fault of a trial, in the simulator's running operation index (relia_ntt_sim.cpp:185-189, 216-220): ops
+ * [0, s1) are the butterflies of the n1 length-n2 transforms of stage 1 in loop order, [s1, s1 + N) the twiddle
+ * products of stage 2, [s1 + N, total) the butterflies of stage 3 (b200fhe_relia_op_ranges).  The product of that
+ * operation becomes (v XOR payload) mod q (kind 1: SBF / DBF, :114-127) or payload mod q (kind 2: MLF, :128-130). */
+typedef struct b200fhe_relia_fault {
+    uint32_t trial;
+    uint32_t kind;
+    uint64_t op;
+    uint64_t payload;
+} b200fhe_relia_fault;
+
+/* End of each stage's operation range for N = n1 n2 (n1 = n2 = sqrt N, N an even power of two). */
+int b200fhe_relia_op_ranges(size_t N, uint64_t* s1_end, uint64_t* s2_end, uint64_t* s3_end);
+
+/* four_step_ntt(N, plan, rng) (relia_ntt_sim.cpp:295-361) for `trials` independent inputs, one CTA each: cyclic
+ * transform with root g^((q-1)/N), stage-1 batch check (:235-274), twiddle stage with the fold-checksum intra check
+ * (:135-142, :208-232; fold_bits = the simulator's --fold-bits) and the inter check (:276-292), stage-3 batch check.
+ * h_in [trials][N]; h_out [trials][N] (optional) = the simulator's C_transposed; h_weights [trials][2 n2 + n1] = the
+ * random check weights the simulator draws with rng.rand_q(): w of batch 1 (n2), phi (n2), w of batch 2 (n1).
+ * h_flags[t]: bit 0 = batch 1 failed, bit 1 = intra fired, bit 2 = inter failed, bit 3 = batch 2 failed; the
+ * simulator's `detected` (:359) is h_flags[t] != 0.  N <= 4096. */
+int b200fhe_relia_four_step_host(uint64_t q, uint64_t g, size_t N, int fold_bits, const uint64_t* h_in, uint64_t* h_out,
+                                 const uint64_t* h_weights, size_t trials, const b200fhe_relia_fault* faults, size_t n_faults,
+                                 uint32_t* h_flags, int device);
 
 /* ---- ct x pt multiply-accumulate (config C3) ------------------------------- */
 

@@ -16,18 +16,40 @@ _LIB = None
 U64P = C.POINTER(C.c_uint64)
 
 
-def build(force=False):
+def _host_tag():
+    """Identifies the host CPU (model + ISA flags): a -march=native object must never run on another machine."""
+    import hashlib
+    try:
+        txt = open("/proc/cpuinfo").read()
+        key = "".join(l for l in txt.splitlines() if l.startswith(("model name", "flags")))[:20000]
+    except OSError:
+        key = "unknown"
+    return hashlib.sha1(key.encode()).hexdigest()[:10]
+
+
+def build(force=False, native=False):
+    """Portable build (x86-64-v3, `make`), or with native=True a -march=native build for THIS host's cores (the timed CPU arm
+    of bench.py).  The native object carries the host's CPU tag in its name; falls back to the portable one."""
     so = os.path.join(_HERE, "liboracle.so")
     src = os.path.join(_HERE, "ntt_oracle.c")
     if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
+    if native:
+        nso = os.path.join(_HERE, "liboracle_native_%s.so" % _host_tag())
+        try:
+            if force or not os.path.exists(nso) or os.path.getmtime(nso) < os.path.getmtime(src):
+                subprocess.check_call(["/usr/bin/gcc", "-O3", "-march=native", "-fopenmp", "-fPIC", "-shared", "-o", nso, src],
+                                      stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            return nso
+        except (OSError, subprocess.CalledProcessError):
+            pass
     return so
 
 
 def lib():
     global _LIB
     if _LIB is None:
-        L = C.CDLL(build())
+        L = C.CDLL(build(native=os.environ.get("ORACLE_NATIVE") == "1"))
         u64, i32 = C.c_uint64, C.c_int
         for name, res, args in [
             ("orc_mulmod", u64, [u64, u64, u64]),
@@ -50,6 +72,11 @@ def lib():
             ("orc_ntt_inverse_harvey", None, [U64P, i32, u64, U64P, U64P]),
             ("orc_ntt_forward_batch", None, [U64P, i32, i32, U64P, U64P, U64P]),
             ("orc_ntt_inverse_batch", None, [U64P, i32, i32, U64P, U64P, U64P]),
+            ("orc_ntt_forward_polys", None, [U64P, i32, i32, i32, U64P, U64P, U64P]),
+            ("orc_ntt_inverse_polys", None, [U64P, i32, i32, i32, U64P, U64P, U64P]),
+            ("orc_relia_four_step", i32, [u64, u64, i32, i32, U64P, U64P, U64P, C.c_void_p, i32]),
+            ("orc_set_threads", None, [i32]),
+            ("orc_get_threads", i32, []),
             ("orc_abft_weights", None, [i32, U64P]),
             ("orc_abft_output_weights", None, [i32, u64, U64P, U64P, U64P]),
             ("orc_ntt_forward_protected", i32, [U64P, i32, u64, U64P, U64P, U64P, C.c_void_p, i32, U64P, U64P]),
@@ -124,15 +151,29 @@ def ntt_inverse(a, tab, kind="harvey"):
     return a
 
 
+class BatchTables:
+    """The per-modulus tables of a limb range stacked ONCE ([L][N] each), for the batched drivers."""
+
+    def __init__(self, tabs):
+        self.tabs = list(tabs)
+        self.logn, self.L = self.tabs[0].logn, len(self.tabs)
+        self.q = np.array([t.q for t in self.tabs], dtype=np.uint64)
+        self.rp = np.stack([t.rp for t in self.tabs]); self.rps = np.stack([t.rps for t in self.tabs])
+        self.irp = np.stack([t.irp for t in self.tabs]); self.irps = np.stack([t.irps for t in self.tabs])
+
+
+def _batch(tabs):
+    return tabs if isinstance(tabs, BatchTables) else BatchTables(tabs)
+
+
 def ntt_forward_batch(a, tabs, inplace=False):
-    """a: [L][N]; limb l uses tabs[l]."""
+    """a: [L][N] or [P][L][N]; limb l of every polynomial uses tabs[l] (a list of Tables, or a BatchTables built once)."""
     a = np.ascontiguousarray(a, dtype=np.uint64)
     if not inplace:
         a = a.copy()
-    L = len(tabs)
-    q = np.array([t.q for t in tabs], dtype=np.uint64)
-    rp = np.stack([t.rp for t in tabs]); rps = np.stack([t.rps for t in tabs])
-    lib().orc_ntt_forward_batch(_p(a), tabs[0].logn, L, _p(q), _p(rp), _p(rps))
+    b = _batch(tabs)
+    assert a.shape[-2] == b.L
+    lib().orc_ntt_forward_polys(_p(a), b.logn, b.L, a.size >> b.logn, _p(b.q), _p(b.rp), _p(b.rps))
     return a
 
 
@@ -140,11 +181,16 @@ def ntt_inverse_batch(a, tabs, inplace=False):
     a = np.ascontiguousarray(a, dtype=np.uint64)
     if not inplace:
         a = a.copy()
-    L = len(tabs)
-    q = np.array([t.q for t in tabs], dtype=np.uint64)
-    irp = np.stack([t.irp for t in tabs]); irps = np.stack([t.irps for t in tabs])
-    lib().orc_ntt_inverse_batch(_p(a), tabs[0].logn, L, _p(q), _p(irp), _p(irps))
+    b = _batch(tabs)
+    assert a.shape[-2] == b.L
+    lib().orc_ntt_inverse_polys(_p(a), b.logn, b.L, a.size >> b.logn, _p(b.q), _p(b.irp), _p(b.irps))
     return a
+
+
+def set_threads(n=None):
+    """Pin the OpenMP thread count of the batched drivers (default: every host core) and return what is in force."""
+    lib().orc_set_threads(int(n) if n else (os.cpu_count() or 1))
+    return int(lib().orc_get_threads())
 
 
 class OrcInject(C.Structure):
@@ -366,3 +412,21 @@ def ct_tensor(a, b, moduli):
     d2 = pmult_accum(a[1][None, None], b[1][None], moduli)[0]
     d1 = pmult_accum(np.stack([a[0], a[1]])[:, None], np.stack([b[1], b[0]]), moduli)[0]
     return np.stack([d0, d1, d2])
+
+
+class OrcReliaFault(C.Structure):
+    _fields_ = [("op", C.c_uint64), ("kind", C.c_uint32), ("pad", C.c_uint32), ("payload", C.c_uint64)]
+
+
+def relia_four_step(q, g, a, weights, faults=(), fold_bits=4):
+    """One trial of relia_ntt_sim.cpp four_step_ntt: a [N], weights [2 n2 + n1], faults (op, kind, payload).
+    Returns (out [N], flags): bit 0 batch 1 failed, 1 intra, 2 inter, 3 batch 2."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    weights = np.ascontiguousarray(weights, dtype=np.uint64)
+    faults = list(faults)
+    arr = (OrcReliaFault * max(len(faults), 1))()
+    for i, (op, kind, payload) in enumerate(faults):
+        arr[i] = OrcReliaFault(int(op), int(kind), 0, int(payload))
+    out = np.zeros_like(a)
+    flags = lib().orc_relia_four_step(q, g, a.size, fold_bits, _p(a), _p(out), _p(weights), C.cast(arr, C.c_void_p), len(faults))
+    return out, int(flags)
