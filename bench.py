@@ -39,32 +39,73 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_reference(steps, warmup, sample_polys=1):
-    """Oracle (restated SEAL Harvey NTT) on all host cores: fwd+inv of
-    sample_polys x 36 limbs per step."""
+def cpu_reference(steps, warmup, sample_polys=NPOLY):
+    """Oracle (restated SEAL Harvey NTT) on ALL host cores: fwd+inv of sample_polys x 36 limbs per step, the same batch
+    shape the GPU arm times.  Tables are stacked once (outside the timed loop); the OpenMP thread count is set explicitly
+    (torchrun exports OMP_NUM_THREADS=1) and reported; the object is built with -march=native for this host."""
+    os.environ.setdefault("ORACLE_NATIVE", "1")
     from oracle import oracle as O
-    cores = os.cpu_count() or 1
+    threads = O.set_threads(os.cpu_count() or 1)
     moduli = O.primes_create(N, [BITS] * L)
-    tabs = [O.Tables(LOG_N, q) for q in moduli]
+    bt = O.BatchTables([O.Tables(LOG_N, q) for q in moduli])
     a = np.stack([O.uniform_limbs(moduli, N, seed=SEED + i) for i in range(sample_polys)])
     ref = a.copy()
     def step():
-        for i in range(sample_polys):
-            O.ntt_forward_batch(a[i], tabs, inplace=True)
-        for i in range(sample_polys):
-            O.ntt_inverse_batch(a[i], tabs, inplace=True)
+        O.ntt_forward_batch(a, bt, inplace=True)
+        O.ntt_inverse_batch(a, bt, inplace=True)
     for _ in range(warmup):
         step()
     if steps is None:                       # size the sample to about 10 s of CPU work
         t0 = time.perf_counter(); step(); one = time.perf_counter() - t0
-        steps = int(min(2000, max(5, 10.0 / max(one, 1e-6))))
+        steps = int(min(2000, max(3, 10.0 / max(one, 1e-6))))
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
     dt = time.perf_counter() - t0
     assert np.array_equal(a, ref), "oracle round trip failed"
     per_step = 2 * sample_polys * L
-    return per_step * steps / dt, dt / steps * 1e3, cores, "%d poly x %d limbs fwd+inv per step, %d steps" % (sample_polys, L, steps)
+    lib_name = os.path.basename(O.lib()._name)
+    return per_step * steps / dt, dt / steps * 1e3, threads, ("%d polys x %d limbs fwd+inv per step (%d limb-transforms), %d steps, %d OpenMP threads, %s"
+                                                                % (sample_polys, L, per_step, steps, threads, lib_name))
+
+
+def newest_ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of each pass kernel, parsed from the newest committed
+    profiles/*_ncu_full_summary.txt (ncu --set full of this same command; profiles/ncu_summary.py wrote it)."""
+    import ast, glob, re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_full_summary.txt")), key=lambda f: (os.path.getmtime(f), f))
+    for f in reversed(files):
+        rows = {}
+        for line in open(f):
+            m = re.match(r"(Kernel Name|dram__bytes_read\.sum|dram__bytes_write\.sum)\s+(\[.*\])\s*$", line)
+            if m:
+                rows[m.group(1)] = ast.literal_eval(m.group(2))
+        if len(rows) == 3:
+            out = {}
+            for name, r, w in zip(rows["Kernel Name"], rows["dram__bytes_read.sum"], rows["dram__bytes_write.sum"]):
+                for k in ("k_fwd_col", "k_fwd_row", "k_inv_row", "k_inv_col"):
+                    if k in name:
+                        out[k] = (float(r) + float(w)) * 1e6      # the summary is in MB; the last (largest-batch) launch wins
+            if out:
+                return out, os.path.relpath(f, ROOT)
+    return {}, None
+
+
+def measured_butterfly_cycles():
+    """Best VALID register-only rate of the product's butterfly form (cycles per warp-butterfly per sub-partition) from the
+    newest committed microbenchmark output under profiles/microbench/."""
+    import glob, re
+    best, src = None, None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "microbench", "*butterfly*.txt")), key=lambda f: (os.path.getmtime(f), f))
+    for f in reversed(files):
+        for line in open(f):
+            if line.startswith("V2") and "cyc/warp-butterfly/SMSP=" in line:
+                v = float(line.rsplit("=", 1)[1])
+                if best is None or v < best:
+                    best, src = v, os.path.relpath(f, ROOT)
+        if best is not None:
+            break
+    return best, src
 
 
 class ClockSampler:
@@ -107,6 +148,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--npoly", type=int, default=NPOLY)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="skip the pmult / ModUp / key-switch sub-records")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -119,7 +161,7 @@ def main():
         if rank != 0:
             return
         steps = max(1, min(args.steps, 20)); warm = max(1, min(args.warmup, 3))
-        v, ms, cores, sample = cpu_reference(steps, warm)
+        v, ms, cores, sample = cpu_reference(steps, warm, args.npoly)
         print(json.dumps({"impl": "reference", "metric": "NTT limb-transforms/s", "value": v, "unit": "limb-transforms/s",
                           "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
@@ -159,14 +201,14 @@ def main():
     # correctness gate before timing: forward of poly 0 vs oracle, then round trip
     from oracle import oracle as O
     NOCHECK = bool(os.environ.get("B200_BENCH_NOCHECK"))   # timing ablations of deliberately wrong kernels
-    if rank == 0 and not NOCHECK:
-        pkg.binding.check(lib.b200fhe_nwt_forward(ctx._h, dp, 1, L, 0, sp))
-        got = d[:L * N].cpu().numpy().view(np.uint64).reshape(L, N)
-        tabs3 = {l: O.Tables(LOG_N, moduli[l]) for l in (0, 35)}
-        for l, t in tabs3.items():
-            assert np.array_equal(got[l], O.ntt_forward(ref0[l], t)), "GPU forward != oracle (limb %d)" % l
-        pkg.binding.check(lib.b200fhe_nwt_backward(ctx._h, dp, 1, L, 0, sp))
-        assert np.array_equal(d[:L * N].cpu().numpy().view(np.uint64).reshape(L, N), ref0), "round trip failed"
+    if rank == 0 and not NOCHECK:          # every limb of two polynomials of the batch against the oracle, then the round trip
+        ncheck = min(2, npoly)
+        bt = O.BatchTables([O.Tables(LOG_N, q) for q in moduli])
+        pkg.binding.check(lib.b200fhe_nwt_forward(ctx._h, dp, npoly, L, 0, sp))
+        got = d[:ncheck * L * N].cpu().numpy().view(np.uint64).reshape(ncheck, L, N)
+        assert np.array_equal(got, O.ntt_forward_batch(hv[:ncheck], bt)), "GPU forward != oracle"
+        pkg.binding.check(lib.b200fhe_nwt_backward(ctx._h, dp, npoly, L, 0, sp))
+        assert np.array_equal(d.cpu().numpy().view(np.uint64).reshape(npoly, L, N), hv), "round trip failed"
 
     def barrier():
         if world > 1:
@@ -235,20 +277,19 @@ def main():
     # one pass kernel = half of a limb-transform's 16 B/coeff (the pair shares the 1 MiB)
     algo_bytes_launch = npoly * L * ALGO_BYTES_PER_LIMB_TRANSFORM / 2
     ach = algo_bytes_launch / (kern[dom] * 1e-3) / 1e9
-    # dram__bytes_read.sum + dram__bytes_write.sum per whole-batch launch, from the committed ncu --set full capture of this
-    # same command (profiles/r1f_ncu_full_summary.txt; npoly=8): MB read + MB written
-    NCU_TRAFFIC = {"k_fwd_col": (151.18 + 91.23) * 1e6, "k_fwd_row": (188.78 + 98.55) * 1e6,
-                   "k_inv_row": (188.78 + 93.93) * 1e6, "k_inv_col": (151.18 + 91.21) * 1e6}
+    traffic, traffic_src = newest_ncu_traffic()
+    bf_cyc, bf_src = measured_butterfly_cycles()
+    sm_hz = 1e6 * (clocks.get("sm_mhz") or 1965.0) if clocks else 1.965e9
     roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": NCU_TRAFFIC[dom] if npoly == NPOLY else None,
-            "traffic_source": "profiles/r1f_ncu_full_summary.txt (ncu --set full, same command, per launch)",
+            "traffic": traffic.get(dom) if npoly == NPOLY else None,
+            "traffic_source": (traffic_src + " (ncu --set full of this command, dram bytes read + written per launch; parsed at run time)") if traffic_src else None,
             "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes_launch,
             "kernel_ms": kern, "note": "one pass kernel over the whole batch = half of a transform's 16 B/coeff; "
-            "transform_frac = limb-transforms/s x 1 MiB / peak.  The kernels are bound by the integer-multiply pipe "
-            "(sm__pipe_fmaheavy 70-76 % busy in the same capture), not by HBM: DESIGN.md section 6",
+            "transform_frac = limb-transforms/s x 1 MiB / peak.  The kernels are bound by the integer-multiply pipe, not by HBM: DESIGN.md section 6",
             "transform_frac": value / world * ALGO_BYTES_PER_LIMB_TRANSFORM / 1e9 / peak,
-            "integer_pipe": {"fmaheavy_busy_pct_ncu": {"k_fwd_col": 75.9, "k_fwd_row": 70.0, "k_inv_row": 71.5, "k_inv_col": 75.0},
-                             "ceiling_limb_transforms_per_s_at_100pct": 2.73e6}}
+            "integer_pipe": {"measured_cycles_per_warp_butterfly": bf_cyc, "source": bf_src,
+                             "ceiling_limb_transforms_per_s": (592 * sm_hz / (N // 64 * LOG_N * bf_cyc)) if bf_cyc else None,
+                             "note": "register-only microbenchmark of the product's butterfly form; N/64 x log2 N warp-butterflies per limb-transform over 592 sub-partitions at the sampled SM clock"}}
 
     # e2e: host buffers through the C ABI (H2D + kernels + D2H per call)
     hp = hv.ctypes.data_as(C.POINTER(C.c_uint64))
@@ -271,6 +312,17 @@ def main():
     assert NOCHECK or np.array_equal(hv[0], ref0), "e2e round trip failed"
     bytes_dir = 2 * npoly * L * N * 8      # fwd call + inv call, each copies the batch in and out
 
+    # the other BASELINE configs, measured in this same process (every rank runs them; rank 0 reports its own)
+    sub = {}
+    if not args.no_sub:
+        import bench_sub
+        del d
+        torch.cuda.empty_cache()
+        sub["pmult"] = bench_sub.pmult_record(pkg, torch, O, peak, local, check=not NOCHECK)
+        sub["modup"], sub["keyswitch"] = bench_sub.keyswitch_records(pkg, torch, O, peak, local, check=not NOCHECK)
+        if world > 1:
+            barrier()
+
     if rank == 0:
         out = {"metric": "NTT limb-transforms/s", "value": value, "unit": "limb-transforms/s", "n_gpus": world,
                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
@@ -279,6 +331,7 @@ def main():
                "e2e": {"value": e2e_val, "unit": "limb-transforms/s", "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir,
                        "steps": e2e_steps, "timer": "host perf_counter around synchronous C-ABI calls, max over ranks"},
                "roofline": roof, "abft": abft}
+        out.update(sub)
         if world == 1 and not args.no_cpu_baseline:
             v, ms, cores, sample = cpu_reference(None, 1)      # about 10 s of host work
             out["cpu_baseline"] = {"value": v, "unit": "limb-transforms/s", "cores": cores, "kind": "port", "sample": sample}

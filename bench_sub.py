@@ -1,0 +1,135 @@
+"""Sub-records of bench.py's JSON line: the other BASELINE configs measured in the same driver-run
+process as the headline, each with its time, its roofline fraction and a parity flag against the oracle.
+
+  pmult      C3  sum of 64 ct x pt, N=2^16, L=36, 2 polys per ciphertext          (HBM-bound)
+  modup      C5  key-switch ModUp of one polynomial, N=2^17, 48 + 16 limbs, dnum=3  (integer/tensor bound; 1 GPU: CUDA graph)
+  keyswitch  f1  whole hybrid key-switch at C5's shape                             (same)
+
+All device-resident, CUDA events on the launching stream, inputs larger than L2 or rewritten every step.
+The oracle (test infrastructure) is used here as the checker only."""
+import numpy as np
+
+
+def _timed(torch, fn, steps, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    st = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(steps):
+        fn()
+    e1.record(st)
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def _graphed(torch, fn):
+    """fn replayed as one CUDA graph, or None when capture is not possible"""
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        return g.replay
+    except Exception:
+        torch.cuda.synchronize()
+        return None
+
+
+def pmult_record(pkg, torch, O, peak, device, steps=10, check=True):
+    log_n, L, T, P = 16, 36, 64, 2
+    N = 1 << log_n
+    moduli = pkg.primes_create(N, [60] * L)
+    ctx = pkg.Context(log_n, moduli, device=device)
+    g = torch.Generator(device="cuda").manual_seed(20250606)
+    ct = torch.randint(0, 1 << 59, (T, P, L, N), dtype=torch.int64, device="cuda", generator=g)
+    pt = torch.randint(0, 1 << 59, (T, L, N), dtype=torch.int64, device="cuda", generator=g)
+    out = torch.zeros((P, L, N), dtype=torch.int64, device="cuda")
+    cps = [ct[k].data_ptr() for k in range(T)]
+    pps = [pt[k].data_ptr() for k in range(T)]
+    l0 = pkg.lib().b200fhe_launch_count()
+    sp = lambda: torch.cuda.current_stream().cuda_stream
+    ctx.pmult_accum(cps, pps, out.data_ptr(), P, L=L, stream=sp())
+    torch.cuda.synchronize()
+    launches = int(pkg.lib().b200fhe_launch_count() - l0)
+    parity = None
+    if check:      # every limb, both polynomials, a window of 1024 coefficients per limb (the full-size comparison is tests/test_baseline_shapes_gpu.py)
+        w0, w1 = 4096, 4096 + 1024
+        cth = np.ascontiguousarray(ct[:, :, :, w0:w1].cpu().numpy().view(np.uint64))
+        pth = np.ascontiguousarray(pt[:, :, w0:w1].cpu().numpy().view(np.uint64))
+        want = O.pmult_accum(cth, pth, moduli)
+        parity = bool(np.array_equal(out[:, :, w0:w1].cpu().numpy().view(np.uint64), want))
+    ms = _timed(torch, lambda: ctx.pmult_accum(cps, pps, out.data_ptr(), P, L=L, stream=sp()), steps)
+    algo = (3 * T + 2) * L * N * 8
+    rec = {"workload": "C3: sum of 64 ct x pt, N=2^16, L=36, 2 polys per ct (dotprod_test.cu shape)", "ms": ms, "launches_per_call": launches,
+           "value": T / (ms * 1e-3), "unit": "ct*pt terms/s",
+           "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": algo / (ms * 1e-3) / 1e9 / peak,
+                        "algorithmic_bytes_per_call": algo},
+           "parity_vs_oracle": parity, "parity_scope": "36 limbs x 2 polys x 1024 coefficients, bit-exact"}
+    del ct, pt, out
+    return rec
+
+
+def keyswitch_records(pkg, torch, O, peak, device, steps=10, check=True):
+    """(modup record, keyswitch record) at C5's shape on one GPU."""
+    log_n, n_q, n_p, dnum = 17, 48, 16, 3
+    N, total, alpha = 1 << log_n, n_q + n_p, n_q // dnum
+    moduli = pkg.primes_create(N, [60] * total)
+    ctx = pkg.Context(log_n, moduli, device=device)
+    ks = pkg.KeySwitch(ctx, n_q, n_p, dnum)
+    rng = np.random.default_rng(20250606)
+    c = np.stack([rng.integers(0, q, size=N, dtype=np.uint64) for q in moduli[:n_q]])
+    evk = np.stack([rng.integers(0, q, size=(dnum, 2, N), dtype=np.uint64) for q in moduli]).transpose(1, 2, 0, 3).copy()   # [dnum][2][total][N]
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.int64)).cuda()
+    d_c, d_eq, d_ep = dev(c), dev(evk[:, :, :n_q]), dev(evk[:, :, n_q:])
+    d_out = torch.zeros((2, n_q, N), dtype=torch.int64, device="cuda")
+    d_up = torch.zeros((dnum, total, N), dtype=torch.int64, device="cuda")
+    sp = lambda: torch.cuda.current_stream().cuda_stream
+    lib = pkg.lib()
+    l0 = lib.b200fhe_launch_count()
+    ks.modup(d_c.data_ptr(), d_up.data_ptr(), stream=sp())
+    l1 = lib.b200fhe_launch_count()
+    ks.apply(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr(), stream=sp())
+    torch.cuda.synchronize()
+    l2 = lib.b200fhe_launch_count()
+    par_up = par_ks = None
+    if check:
+        tabs = [O.Tables(log_n, q) for q in moduli]
+        got_up = d_up.cpu().numpy().view(np.uint64)
+        coeff = O.ntt_inverse_batch(c[:alpha], tabs[:alpha])                       # digit 0, every target limb
+        tl = list(range(alpha, total))
+        conv = O.bconv_hps(coeff, moduli[:alpha], [moduli[g] for g in tl])
+        par_up = bool(np.array_equal(got_up[0][tl], O.ntt_forward_batch(conv, [tabs[g] for g in tl])) and np.array_equal(got_up[0][:alpha], c[:alpha]))
+        want = O.keyswitch_hybrid(c, evk, moduli, n_q, n_p, dnum, tabs)
+        par_ks = bool(np.array_equal(want, d_out.cpu().numpy().view(np.uint64)))
+    f_up = lambda: ks.modup(d_c.data_ptr(), d_up.data_ptr(), stream=sp())
+    f_ks = lambda: ks.apply(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr(), stream=sp())
+    g_up, g_ks = _graphed(torch, f_up), _graphed(torch, f_ks)
+    ms_up = _timed(torch, g_up or f_up, steps)
+    ms_ks = _timed(torch, g_ks or f_ks, steps)
+    t_up = n_q + dnum * (total - alpha)
+    mm_up = dnum * alpha * (1 + total - alpha) * N
+    t_ks = t_up + 2 * n_p + 2 * n_q
+    mm_ks = mm_up + 2 * n_p * (1 + n_q) * N
+    # algorithmic HBM bytes: each limb-transform 16 N, base conversion reads m and writes K limbs per digit, inner product streams the key once
+    b_up = (t_up * 16 * N) + dnum * (alpha + total - alpha) * N * 8
+    b_ks = b_up + (2 * n_p + 2 * n_q) * 16 * N + 2 * (n_p + n_q) * N * 8 + (dnum * 3 * total + 2 * total) * N * 8
+    rec_up = {"workload": "C5: key-switch ModUp of one polynomial (INTT + HPS conversion + NTT), N=2^17, 48 + 16 limbs, dnum=3, 1 GPU",
+              "ms": ms_up, "cuda_graph": g_up is not None, "launches_per_call": int(l1 - l0), "value": 1e3 / ms_up, "unit": "polys/s",
+              "work_per_call": {"limb_transforms": t_up, "bconv_mulmods": mm_up},
+              "roofline": {"bound": "hbm", "achieved": b_up / (ms_up * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": b_up / (ms_up * 1e-3) / 1e9 / peak,
+                           "algorithmic_bytes_per_call": b_up, "note": "integer-multiplier / tensor-pipe bound in practice (DESIGN.md 5.5)"},
+              "parity_vs_oracle": par_up, "parity_scope": "digit 0: all 64 limbs, bit-exact (all digits: tests/test_baseline_shapes_gpu.py)"}
+    rec_ks = {"workload": "f1: hybrid key-switch (ModUp, evk inner product, ModDown), N=2^17, 48 + 16 limbs, dnum=3, 1 GPU",
+              "ms": ms_ks, "cuda_graph": g_ks is not None, "launches_per_call": int(l2 - l1), "value": 1e3 / ms_ks, "unit": "key-switches/s",
+              "work_per_call": {"limb_transforms": t_ks, "bconv_mulmods": mm_ks},
+              "roofline": {"bound": "hbm", "achieved": b_ks / (ms_ks * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": b_ks / (ms_ks * 1e-3) / 1e9 / peak,
+                           "algorithmic_bytes_per_call": b_ks},
+              "parity_vs_oracle": par_ks, "parity_scope": "both output polynomials, all 48 limbs, bit-exact against the oracle composition"}
+    ks.close()
+    return rec_up, rec_ks

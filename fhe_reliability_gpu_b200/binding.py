@@ -45,6 +45,7 @@ SIGNATURES = {
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_bconv_create": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, C.POINTER(vp)]),
     "b200fhe_bconv_create_scaled": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, u64, C.POINTER(vp)]),
+    "b200fhe_bconv_create_mode": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, i32, C.POINTER(vp)]),
     "b200fhe_bconv_destroy": (i32, [vp]),
     "b200fhe_bconv_scale": (i32, [vp, vp, vp, sz, sz, vp]),
     "b200fhe_bconv_contract": (i32, [vp, vp, vp, sz, sz, vp]),
@@ -249,12 +250,18 @@ Context.pmult_accum = _pmult_accum
 class BaseConv:
     """ModUp plan (b200fhe_bconv): source base = context moduli src_idx, targets = context moduli dst_idx."""
 
-    def __init__(self, ctx, src_idx, dst_idx, scale=1):
+    HPS, EXACT = 0, 1
+
+    def __init__(self, ctx, src_idx, dst_idx, scale=1, mode=0):
         self.ctx, self.src, self.dst = ctx, list(src_idx), list(dst_idx)
         self.m, self.K, self.N = len(self.src), len(self.dst), ctx.N
         h = vp()
-        check(lib().b200fhe_bconv_create_scaled(ctx._h, (i32 * self.m)(*self.src), self.m, (i32 * self.K)(*self.dst), self.K, scale,
-                                                C.byref(h)))
+        if mode:
+            assert scale == 1, "the exact-CRT mode has no scaled flavour"
+            check(lib().b200fhe_bconv_create_mode(ctx._h, (i32 * self.m)(*self.src), self.m, (i32 * self.K)(*self.dst), self.K, mode, C.byref(h)))
+        else:
+            check(lib().b200fhe_bconv_create_scaled(ctx._h, (i32 * self.m)(*self.src), self.m, (i32 * self.K)(*self.dst), self.K, scale,
+                                                    C.byref(h)))
         self._h = h
 
     def close(self):

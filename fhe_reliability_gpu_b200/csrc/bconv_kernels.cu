@@ -519,6 +519,58 @@ int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* 
     return 0;
 }
 
+// ---- exact-CRT mode (motivation/baseConv.py:67-83 base_conv_fixed) --------------------------------------------------
+// The fast conversion returns x + e P with e = floor(sum_j y_j / p_j) in [0, m).  The exact flavour takes e P out again.
+// e has to be EXACT (a floating-point estimate of sum_j y_j / p_j cannot separate x = 0..few from e - tiny), so it is
+// found in multi-word integers: S = sum_j y_j (P/p_j)  (m words: 60 m + log2 m <= 64 m bits) is compared with the
+// multiples e P; then out_k -= (e P mod q_k).  One thread per coefficient; a mode, not the hot path (the key-switch
+// wants the fast flavour, whose overshoot it absorbs as noise).
+constexpr int kExactMaxM = 64;
+__global__ void __launch_bounds__(128) k_bconv_exact_fix(const u64* __restrict__ y, u64* __restrict__ out, u32 N, u32 m, u32 K,
+                                                         const u64* __restrict__ hatw /*[m][m]*/, const u64* __restrict__ ePw /*[m][m]*/,
+                                                         const u64* __restrict__ ePq /*[K][m]*/, const B200Mod* mods, const u32* dst_idx) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    u64 S[kExactMaxM];
+    for (u32 t = 0; t < m; t++) S[t] = 0;
+    for (u32 j = 0; j < m; j++) {
+        const u64 yj = y[(size_t)j * N + i];
+        const u64* h = hatw + (size_t)j * m;
+        u64 carry = 0;
+        for (u32 t = 0; t < m; t++) {                 // S += yj * h, word by word
+            const u64 lo = yj * h[t], hi = __umul64hi(yj, h[t]);
+            u64 s = S[t] + lo;
+            u64 c = s < lo;
+            s += carry;
+            c += s < carry;
+            S[t] = s;
+            carry = hi + c;                           // hi <= 2^64 - 2, c <= 2: cannot wrap past 2^64 given the bound on S
+        }
+    }
+    u32 e = 0;
+    for (u32 c = m - 1; c >= 1; c--) {                // largest e with e P <= S
+        const u64* w = ePw + (size_t)c * m;
+        bool ge = true;
+        for (int t = (int)m - 1; t >= 0; t--) {
+            if (S[t] != w[t]) { ge = S[t] > w[t]; break; }
+        }
+        if (ge) { e = c; break; }
+    }
+    if (e == 0) return;
+    for (u32 k = 0; k < K; k++) {
+        const u64 q = mods[dst_idx[k]].q, sub = ePq[(size_t)k * m + e];
+        u64 v = out[(size_t)k * N + i];
+        v = v >= sub ? v - sub : v + q - sub;
+        out[(size_t)k * N + i] = v;
+    }
+}
+int launch_bconv_exact_fix(const u64* y, u64* out, u32 N, u32 m, u32 K, const u64* hatw, const u64* ePw, const u64* ePq, const B200Mod* mods,
+                           const u32* dst_idx, cudaStream_t s) {
+    if (m > (u32)kExactMaxM) return -1;
+    k_bconv_exact_fix<<<(N + 127) / 128, 128, 0, s>>>(y, out, N, m, K, hatw, ePw, ePq, mods, dst_idx);
+    return 0;
+}
+
 int launch_bconv_scale(const u64* x, u64* y, const B200Mod* mods, const u32* src_idx, const ulonglong2* inv, u32 N, u32 j0, u32 count,
                        cudaStream_t s) {
     if (!count) return 0;

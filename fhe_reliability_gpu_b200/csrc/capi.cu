@@ -649,6 +649,9 @@ extern "C" int b200fhe_bconv_destroy(b200fhe_bconv* p) {
     if (p->d_inv) cudaFree(p->d_inv);
     if (p->d_hat) cudaFree(p->d_hat);
     if (p->d_btab) cudaFree(p->d_btab);
+    if (p->d_hatw) cudaFree(p->d_hatw);
+    if (p->d_ePw) cudaFree(p->d_ePw);
+    if (p->d_ePq) cudaFree(p->d_ePq);
     if (p->d_cnt) cudaFree(p->d_cnt);
     if (p->d_y) cudaFree(p->d_y);
     if (p->d_io) cudaFree(p->d_io);
@@ -739,6 +742,55 @@ extern "C" int b200fhe_bconv_create_scaled(b200fhe_ctx* c, const int* src_idx, i
     return 0;
 }
 
+// Exact-CRT mode (SURVEY 8(b) `mode /*HPS|EXACT*/`; motivation/baseConv.py:67-83 base_conv_fixed): the plan additionally holds
+// P/p_j and the multiples e P as multi-word integers and e P mod q_k; b200fhe_bconv_modup[_host] then return
+// (x mod P) mod q_k exactly instead of (x + e P) mod q_k.
+extern "C" int b200fhe_bconv_create_mode(b200fhe_ctx* c, const int* src_idx, int m, const int* dst_idx, int K, int mode, b200fhe_bconv** out) {
+    if (mode != B200FHE_BCONV_HPS && mode != B200FHE_BCONV_EXACT) return b200_set_err(B200FHE_EINVAL, "bconv_create_mode: mode must be HPS (0) or EXACT (1)");
+    int rc = b200fhe_bconv_create_scaled(c, src_idx, m, dst_idx, K, 1, out);
+    if (rc || mode == B200FHE_BCONV_HPS) return rc;
+    b200fhe_bconv* p = *out;
+    // little-endian multi-word integers, m words each
+    auto mul_small = [&](std::vector<uint64_t>& a, uint64_t f) {
+        uint64_t carry = 0;
+        for (auto& w : a) { nt::u128 t = (nt::u128)w * f + carry; w = (uint64_t)t; carry = (uint64_t)(t >> 64); }
+    };
+    auto mod_small = [&](const std::vector<uint64_t>& a, uint64_t q) {
+        nt::u128 r = 0;
+        for (size_t i = a.size(); i-- > 0;) r = ((r << 64) | a[i]) % q;
+        return (uint64_t)r;
+    };
+    std::vector<uint64_t> hatw((size_t)m * m, 0), ePw((size_t)m * m, 0), ePq((size_t)K * m, 0);
+    std::vector<uint64_t> P(m, 0);
+    P[0] = 1;
+    for (int j = 0; j < m; j++) mul_small(P, c->moduli[src_idx[j]]);
+    for (int j = 0; j < m; j++) {
+        std::vector<uint64_t> h(m, 0);
+        h[0] = 1;
+        for (int i = 0; i < m; i++) if (i != j) mul_small(h, c->moduli[src_idx[i]]);
+        std::copy(h.begin(), h.end(), hatw.begin() + (size_t)j * m);
+    }
+    for (int e = 1; e < m; e++) {
+        std::vector<uint64_t> w = P;
+        mul_small(w, (uint64_t)e);                   // e P < m 2^(60 m) fits m words
+        std::copy(w.begin(), w.end(), ePw.begin() + (size_t)e * m);
+        for (int k = 0; k < K; k++) ePq[(size_t)k * m + e] = mod_small(w, c->moduli[dst_idx[k]]);
+    }
+    cudaError_t e = cudaMalloc(&p->d_hatw, sizeof(uint64_t) * hatw.size());
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_ePw, sizeof(uint64_t) * ePw.size());
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_ePq, sizeof(uint64_t) * ePq.size());
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_hatw, hatw.data(), sizeof(uint64_t) * hatw.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_ePw, ePw.data(), sizeof(uint64_t) * ePw.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p->d_ePq, ePq.data(), sizeof(uint64_t) * ePq.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        b200fhe_bconv_destroy(p);
+        *out = nullptr;
+        return b200_set_err(B200FHE_ECUDA, "bconv_create_mode: %s", cudaGetErrorString(e));
+    }
+    p->mode = B200FHE_BCONV_EXACT;
+    return 0;
+}
+
 extern "C" int b200fhe_bconv_scale(b200fhe_bconv* p, const uint64_t* d_x, uint64_t* d_y, size_t j0, size_t count, void* stream) {
     if (!p || (count && (!d_x || !d_y)) || j0 + count > (size_t)p->m) return b200_set_err(B200FHE_EINVAL, "bconv_scale: bad arguments");
     CK(cudaSetDevice(p->ctx->device));
@@ -768,7 +820,14 @@ extern "C" int b200fhe_bconv_modup(b200fhe_bconv* p, const uint64_t* d_in, uint6
     if (!p) return b200_set_err(B200FHE_EINVAL, "bconv_modup: null plan");
     int rc = b200fhe_bconv_scale(p, d_in, (uint64_t*)p->d_y, 0, p->m, stream);
     if (rc) return rc;
-    return b200fhe_bconv_contract(p, (const uint64_t*)p->d_y, d_out, 0, p->K, stream);
+    rc = b200fhe_bconv_contract(p, (const uint64_t*)p->d_y, d_out, 0, p->K, stream);
+    if (rc || p->mode != B200FHE_BCONV_EXACT) return rc;
+    if (launch_bconv_exact_fix(p->d_y, (u64*)d_out, (u32)p->ctx->N, (u32)p->m, (u32)p->K, p->d_hatw, p->d_ePw, p->d_ePq, p->ctx->d_mods, p->d_dst,
+                               (cudaStream_t)stream))
+        return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup: exact mode supports at most 64 source moduli");
+    g_launches++;
+    CK(cudaGetLastError());
+    return 0;
 }
 
 extern "C" int b200fhe_bconv_modup_host(b200fhe_bconv* p, const uint64_t* h_in, uint64_t* h_out) {

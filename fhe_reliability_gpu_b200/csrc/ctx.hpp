@@ -54,6 +54,9 @@ int launch_bconv_scale(const u64* x, u64* y, const B200Mod* mods, const u32* src
                        cudaStream_t s);
 int launch_bconv_contract(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const u64* hat, u32 N, u32 m, u32 K, u32 k0,
                           u32 kcount, cudaStream_t s);
+// exact-CRT mode: takes the e P overshoot of the fast conversion out of out [K][N] (hatw [m][m] words of P/p_j, ePw [m][m] words of e P, ePq [K][m])
+int launch_bconv_exact_fix(const u64* y, u64* out, u32 N, u32 m, u32 K, const u64* hatw, const u64* ePw, const u64* ePq, const B200Mod* mods,
+                           const u32* dst_idx, cudaStream_t s);
 // tensor-core (byte-split, mma.sync u8) contraction for source bases of at most 16 moduli; btab [8][ceil(m/4)][K][8] fragments
 int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K,
                              u32 k0, u32 kcount, cudaStream_t s);
@@ -107,6 +110,10 @@ struct b200fhe_bconv {
     ulonglong2* d_inv = nullptr;     // [m] (P/p_j)^-1 mod p_j with Shoup quotient
     u64* d_hat = nullptr;            // [K][m] (P/p_j) mod q_k, 30-bit halves packed
     uint2* d_btab = nullptr;         // m <= 16: the same constants as byte-split tensor-core B fragments (bconv_kernels.cu)
+    int mode = 0;                    // 0: fast (HPS) conversion, 1: exact CRT (motivation/baseConv.py:67-83)
+    u64* d_hatw = nullptr;           // exact mode: [m][m] words of P/p_j
+    u64* d_ePw = nullptr;            //             [m][m] words of e P, e = 0..m-1
+    u64* d_ePq = nullptr;            //             [K][m]  e P mod q_k
     u64* d_y = nullptr;              // [m][N] scratch for the single-GPU path
     u64* d_cnt = nullptr;            // checksum counters of the protected path: two sets of 6 m + 2 K words, used alternately
     int cnt_set = 0;

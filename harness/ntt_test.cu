@@ -30,12 +30,18 @@ static void die(const char* what) {
 #define OK(call) do { if ((call) != 0) die(#call); } while (0)
 
 int main(int argc, char** argv) {
-    if (argc < 5) {
-        std::cerr << "Usage: " << argv[0] << " <log_dim> <batch_size> <num_flips> <num_target_symbols>\n";
+    // Two CLIs, both kept: the current one, `<log_dim> <batch_size> <num_flips> <num_target_symbols>`
+    // (ntt_test.cu:201-216), and the earlier 3-argument one that reliability_test/run_bench_test.sh:10 still calls and
+    // exp_log.txt:3-8 records: `<log_dim> <batch_size> <n>` = flip n unique random bits anywhere in the data buffer.
+    if (argc < 4) {
+        std::cerr << "Usage: " << argv[0] << " <log_dim> <batch_size> <num_flips> <num_target_symbols>\n"
+                  << "   or: " << argv[0] << " <log_dim> <batch_size> <num_unique_bit_flips>\n";
         return 1;
     }
+    const bool legacy = argc == 4;
     const size_t log_dim = std::stoul(argv[1]), batch = std::stoul(argv[2]);
-    const int num_flips = std::stoi(argv[3]), num_syms = std::stoi(argv[4]);
+    const int num_flips = legacy ? 1 : std::stoi(argv[3]), num_syms = legacy ? 1 : std::stoi(argv[4]);
+    const long long legacy_bits = legacy ? std::stoll(argv[3]) : 0;
     const bool real_mode = std::getenv("B200FHE_REAL_TEST") != nullptr;   // ntt_real_test: no injection
     if (!real_mode && (num_flips < 1 || num_syms < 1)) {
         std::cerr << "Error: <num_flips> and <num_target_symbols> must be >= 1\n";
@@ -47,12 +53,16 @@ int main(int argc, char** argv) {
         std::cerr << "ERROR: num_flips (" << num_flips << ") exceeds bits per symbol (64).\n";
         return 1;
     }
+    if (legacy && (legacy_bits < 1 || (uint64_t)legacy_bits > total_bits)) {
+        std::cerr << "ERROR: number of bit flips must be in [1, " << total_bits << "]\n";
+        return 1;
+    }
     if ((uint64_t)num_syms > total) {
         std::cerr << "ERROR: num_target_symbols (" << num_syms << ") exceeds total symbols (" << total << ").\n";
         return 1;
     }
     uint64_t seed;
-    if (argc > 5) seed = std::strtoull(argv[5], nullptr, 0);
+    if (!legacy && argc > 5) seed = std::strtoull(argv[5], nullptr, 0);
     else if (const char* e = std::getenv("B200FHE_SEED")) seed = std::strtoull(e, nullptr, 0);
     else seed = std::random_device{}();
     const int bits = std::getenv("B200FHE_PRIME_BITS") ? std::atoi(std::getenv("B200FHE_PRIME_BITS")) : 50;
@@ -73,6 +83,7 @@ int main(int argc, char** argv) {
         for (size_t j = 0; j < dim; j++) h_in[i * dim + j] = dist(rng);
     }
     std::memcpy(h_clean, h_in, total * 8);
+    if (legacy) std::cout << "Doing NTT 2D RADIX8\n";
     OK(b200fhe_nwt_forward_host(ctx, h_clean, 1, batch, 0));
 
     // distinct target words, distinct bit positions inside each (ntt_test.cu:105-123)
@@ -80,7 +91,15 @@ int main(int argc, char** argv) {
     std::uniform_int_distribution<uint64_t> pick_word(0, total - 1);
     std::uniform_int_distribution<int> pick_bit(0, 63);
     size_t n_bits = 0;
-    if (!real_mode) {
+    if (legacy) {
+        // n unique (word, bit) positions over the whole buffer (exp_log.txt:5 "[2D] Flipping 2 unique random bits in the data buffer...")
+        std::set<uint64_t> flipped;
+        std::uniform_int_distribution<uint64_t> pick_pos(0, total_bits - 1);
+        while ((long long)flipped.size() < legacy_bits) flipped.insert(pick_pos(rng));
+        for (uint64_t pos : flipped) h_in[pos / 64] ^= (1ULL << (pos % 64));
+        std::cout << "[2D] Flipping " << flipped.size() << " unique random bits in the data buffer...\n";
+        std::cout << "Doing NTT 2D RADIX8\n";
+    } else if (!real_mode) {
         while ((int)targets.size() < num_syms) targets.insert(pick_word(rng));
         for (uint64_t w : targets) {
             std::set<int> pos;

@@ -236,6 +236,12 @@ int b200fhe_bconv_create(b200fhe_ctx* ctx, const int* src_idx, int m, const int*
  * (BGV ModDown / mod_switch_to_next subtract this so the plaintext mod t survives the division by P); t = 1 is the plain
  * conversion.  t must be invertible modulo every source modulus. */
 int b200fhe_bconv_create_scaled(b200fhe_ctx* ctx, const int* src_idx, int m, const int* dst_idx, int K, uint64_t t, b200fhe_bconv** out);
+/* Conversion mode: HPS = the fast conversion above; EXACT = the exact CRT of motivation/baseConv.py:67-83
+ * (base_conv_fixed): out_k = (x mod P) mod q_k, the e P overshoot removed with e found in exact multi-word integers.  The
+ * mode applies to b200fhe_bconv_modup[_host]; scale / contract (the sharded path) always are the fast flavour. */
+#define B200FHE_BCONV_HPS 0
+#define B200FHE_BCONV_EXACT 1
+int b200fhe_bconv_create_mode(b200fhe_ctx* ctx, const int* src_idx, int m, const int* dst_idx, int K, int mode, b200fhe_bconv** out);
 int b200fhe_bconv_destroy(b200fhe_bconv* plan);
 
 /* Step 1 on `count` source limbs starting at source position j0: d_y[c][i] = d_x[c][i] (P/p_j)^-1 mod p_j,

@@ -430,3 +430,21 @@ def relia_four_step(q, g, a, weights, faults=(), fold_bits=4):
     out = np.zeros_like(a)
     flags = lib().orc_relia_four_step(q, g, a.size, fold_bits, _p(a), _p(out), _p(weights), C.cast(arr, C.c_void_p), len(faults))
     return out, int(flags)
+
+
+def bconv_exact(x, p, qo):
+    """motivation/baseConv.py:67-83 base_conv_fixed restated with Python integers (small cases): x [m][N] mod p_j ->
+    [K][N] = (CRT(x) mod P) mod qo_k."""
+    x = np.asarray(x, dtype=np.uint64)
+    m, N = x.shape
+    P = 1
+    for pj in p:
+        P *= int(pj)
+    hat = [P // int(pj) for pj in p]
+    inv = [pow(hat[j] % int(p[j]), -1, int(p[j])) for j in range(m)]
+    out = np.zeros((len(qo), N), dtype=np.uint64)
+    for i in range(N):
+        v = sum((int(x[j, i]) % int(p[j])) * hat[j] * inv[j] for j in range(m)) % P
+        for k, q in enumerate(qo):
+            out[k, i] = v % int(q)
+    return out

@@ -8,6 +8,7 @@ Sources (reference paths):
   reliability_test/four_step_ntt_prot.py   four_step_ntt, ntt_direct, protection checks, demo(16, 42)
   rfhe_framewk/src/negaclic_ntt.py         negacyclic_ntt / negacyclic_intt / naive negacyclic product / ecc weights
   rfhe_framewk/src/baseConv.py             bConv, bConv_ecc
+  motivation/baseConv.py:67-83             base_conv_fixed (exact CRT conversion)
   motivation/ntt.py:8-32                   inline cyclic radix-2 NTT (restated call; module has plotting side effects)
 Run:  python tests/golden/make_golden.py
 """
@@ -130,6 +131,30 @@ def baseconv():
     dump("baseconv_py.json", {"cases": out})
 
 
+def motivation_baseconv():
+    # motivation/baseConv.py:67-83 base_conv_fixed (the exact-CRT conversion), imported with matplotlib stubbed out
+    # (the module imports pyplot at the top for its plotting demo; the package is not installed here)
+    import types
+    stub = types.ModuleType("matplotlib"); stub.pyplot = types.ModuleType("matplotlib.pyplot")
+    sys.modules.setdefault("matplotlib", stub); sys.modules.setdefault("matplotlib.pyplot", stub.pyplot)
+    mb = load("motivation/baseConv.py", "motivation_baseConv")
+    out = []
+    for m, K, N, bits, seed in [(3, 3, 20, 30, 1), (4, 2, 16, 20, 2), (2, 5, 8, 40, 3), (6, 3, 12, 28, 4)]:
+        random.seed(seed)
+        p = mb.generate_crt_primes(m, bits)
+        qo = mb.generate_crt_primes(K, bits)
+        P = 1
+        for v in p:
+            P *= v
+        values = [random.randint(0, P - 1) for _ in range(N)]
+        values[0], values[1], values[2] = 0, 1, P - 1           # the cases a floating-point estimate of e gets wrong
+        res = mb.values_to_rns(values, p)
+        conv = mb.base_conv_fixed(res, p, qo)
+        assert conv == mb.values_to_rns(values, qo)
+        out.append({"m": m, "K": K, "N": N, "seed": seed, "p": p, "q_out": qo, "residues": res, "base_conv_fixed": conv})
+    dump("motivation_baseconv.json", {"cases": out})
+
+
 def motivation_ntt():
     # motivation/ntt.py:8-32 executed on its own deterministic input (:35-41); the module itself
     # imports matplotlib with a font that is absent, so the function source is exec'd in isolation.
@@ -149,4 +174,5 @@ if __name__ == "__main__":
     four_step()
     negacyclic()
     baseconv()
+    motivation_baseconv()
     motivation_ntt()

@@ -61,6 +61,32 @@ def test_hps_result_is_x_plus_small_multiple_of_P(pkg, O):
         assert len(es) == 1
 
 
+@pytest.mark.parametrize("log_n,bits,m,K", [(4, 30, 2, 3), (10, 50, 3, 5), (12, 60, 16, 7), (12, 60, 1, 2), (11, 60, 40, 3)])
+def test_exact_crt_mode_vs_oracle(pkg, O, log_n, bits, m, K):
+    """b200fhe_bconv_create_mode(..., EXACT): (x mod P) mod q_k as motivation/baseConv.py:67-83, including the values whose
+    overshoot count e a floating-point estimate cannot decide (x = 0, 1, 2, P-1, P-2) and the largest overshoot."""
+    N = 1 << log_n
+    moduli = pkg.primes_create(N, [bits] * (m + K))
+    ctx = pkg.Context(log_n, moduli)
+    p, q = moduli[:m], moduli[m:]
+    P = 1
+    for v in p:
+        P *= v
+    rng = np.random.default_rng(m * 100 + K)
+    vals = [int.from_bytes(rng.bytes(8 * m + 8), "little") % P for _ in range(N)]
+    vals[:5] = [0, 1, 2 % P, P - 1, (P - 2) % P]
+    x = np.array([[v % pj for v in vals] for pj in p], dtype=np.uint64)
+    want = np.array([[v % qk for v in vals] for qk in q], dtype=np.uint64)
+    assert np.array_equal(O.bconv_exact(x[:, :64], p, q), want[:, :64])          # the restatement agrees with plain arithmetic
+    exact = pkg.BaseConv(ctx, list(range(m)), list(range(m, m + K)), mode=pkg.BaseConv.EXACT)
+    assert np.array_equal(exact.modup_host(x), want)
+    fast = pkg.BaseConv(ctx, list(range(m)), list(range(m, m + K)))
+    hps = fast.modup_host(x)
+    assert np.array_equal(hps, O.bconv_hps(x, p, q))
+    if m > 1:
+        assert not np.array_equal(hps, want)                                      # the fast flavour does overshoot somewhere
+
+
 def test_sharded_pipeline_world1_matches_oracle(pkg, O):
     """modup_digit with world = 1 (no collective): INTT -> HPS conversion -> NTT of every digit == oracle composition."""
     import torch

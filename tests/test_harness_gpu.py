@@ -73,13 +73,37 @@ def test_ntt_test_is_reproducible_with_a_seed_and_random_without():
 
 
 def test_ntt_test_argument_errors_exit_1():
-    assert run(NTT_TEST, 12, 1, 1).returncode == 1                      # ntt_test.cu:202-206
-    assert "Usage:" in run(NTT_TEST, 12, 1, 1).stderr
+    assert run(NTT_TEST, 12, 1).returncode == 1                         # ntt_test.cu:202-206 (3 arguments = the legacy CLI below)
+    assert "Usage:" in run(NTT_TEST, 12, 1).stderr
+    assert run(NTT_TEST, 12, 1, 0).returncode == 1
     assert run(NTT_TEST, 12, 1, 0, 1).returncode == 1                   # :213-216
     p = run(NTT_TEST, 12, 1, 65, 1)
     assert p.returncode == 1 and "exceeds bits per symbol (64)" in p.stderr       # :29-33
     p = run(NTT_TEST, 4, 1, 1, 17)
     assert p.returncode == 1 and "exceeds total symbols (16)" in p.stderr         # :34-38
+
+
+@pytest.mark.parametrize("n", [2, 32, 2048])
+def test_legacy_three_argument_cli(n):
+    """reliability_test/run_bench_test.sh:10 `./ntt_test 12 32 $n` (n unique random bit flips anywhere in the buffer) and the
+    lines exp_log.txt:3-8 records for it.  n = 2 hits two limbs: symbol errors 8192/131072, as exp_log.txt:3 shows."""
+    p = run(NTT_TEST, 12, 32, n, env={"B200FHE_SEED": str(1000 + n)})
+    assert p.returncode == 0, p.stderr
+    lines = p.stdout.splitlines()
+    assert lines[0] == "Doing NTT 2D RADIX8"
+    assert lines[1] == "[2D] Flipping %d unique random bits in the data buffer..." % n
+    assert lines[2] == "Doing NTT 2D RADIX8"
+    m = RE_FULL.search(p.stderr)
+    assert m, p.stderr
+    ham, bits, bad, tot = int(m[1]), int(m[2]), int(m[4]), int(m[5])
+    assert bits == 32 * 4096 * 64 and tot == 32 * 4096
+    assert bad % 4096 == 0 and 4096 <= bad <= min(n, 32) * 4096           # every output symbol of each hit limb
+    if n == 2:
+        assert bad in (4096, 8192)
+    if n == 2048:
+        assert bad == 32 * 4096                                             # exp_log.txt: large n corrupts every limb
+    assert 20.0 < ham / bad < 30.0
+    assert "ERROR! Total bitwise Hamming distance = %d (bit error rate = " % ham in p.stdout
 
 
 def test_real_test_mode_reports_all_correct():
