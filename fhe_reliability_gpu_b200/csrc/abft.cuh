@@ -66,12 +66,18 @@ struct AbftOut {
 // k_abft_finalize recombines the digit sums and reduces mod q once per limb.  CTA-uniform call sites only.
 constexpr int kAbftStride = 8;
 constexpr int kAbftDigit = 26;       // 32 lanes x 26-bit digits sum to < 2^31: one 32-bit REDUX per digit
+// grp / n_grp: the CTA's warps may belong to n_grp different limbs (the row passes process several polynomials side by
+// side); the warps [grp * wpg, (grp + 1) * wpg) commit to `limb` of their own group.  Call sites must be uniform per group.
 template <int NDIG>
-__device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u64 s0, u64 s1) {
-    u64* c = counters + ((size_t)limb * 2 + side) * kAbftStride;
+__device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u64 s0, u64 s1, int grp = 0, int n_grp = 1) {
     constexpr u32 mask = (1u << kAbftDigit) - 1u;
 #ifndef B200_ABFT_WARP_COMMIT
     __shared__ u32 red[32][NDIG];        // per-warp digit sums (< 2^31 each); every thread of the CTA calls this
+    __shared__ u32 glimb[4];
+    const u32 wpg = (blockDim.x >> 5) / n_grp;                 // warps per group
+    if ((threadIdx.x & 31) == 0 && (threadIdx.x >> 5) % wpg == 0) glimb[grp] = limb;
+#else
+    u64* c = counters + ((size_t)limb * 2 + side) * kAbftStride;
 #endif
 #ifdef B200_ABL_ABFT_NOCOMMIT        // timing ablation (profiles/microbench/runexp.sh): sums stay live, no REDUX / RED
     if ((s0 ^ s1) != 0x9E3779B97F4A7C15ull) return;
@@ -92,12 +98,14 @@ __device__ __forceinline__ void abft_commit(u64* counters, u32 limb, int side, u
 #endif
     }
 #ifndef B200_ABFT_WARP_COMMIT
-    // one RED per digit per CTA instead of per warp: the counters of a limb are one hot L2 line
+    // one RED per digit per group instead of per warp: the counters of a limb are one hot L2 line
     __syncthreads();
-    if (threadIdx.x < NDIG) {
+    if (threadIdx.x < (u32)(NDIG * n_grp)) {
+        const u32 g = threadIdx.x / NDIG, d = threadIdx.x % NDIG;
         u64 tot = 0;
-        for (u32 w = 0; w < (blockDim.x + 31) / 32; w++) tot += red[w][threadIdx.x];
-        asm volatile("red.global.add.u64 [%0], %1;" ::"l"(c + threadIdx.x), "l"(tot) : "memory");
+        for (u32 w = g * wpg; w < (g + 1) * wpg; w++) tot += red[w][d];
+        u64* c = counters + ((size_t)glimb[g] * 2 + side) * kAbftStride;
+        asm volatile("red.global.add.u64 [%0], %1;" ::"l"(c + d), "l"(tot) : "memory");
     }
 #endif
 }

@@ -30,6 +30,7 @@ struct PassArgs {
     u32 L;                    // limbs per polynomial in this call
     u32 start_mod;
     u32 n_poly = 1;           // polynomials in this launch (grid.x = tiles * n_poly)
+    u32 poly0 = 0;            // row passes: first polynomial of this launch (an odd last polynomial of a batch runs the one-poly form)
     // protected (ABFT) forward transform only
     const u64* omega = nullptr;     // [ctx.L][N] output weights, 30-bit halves packed (lo | hi << 32)
     u64* abft = nullptr;            // [n_limbs of the call][2][4] digit-sum counters

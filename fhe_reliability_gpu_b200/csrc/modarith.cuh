@@ -70,30 +70,36 @@ __device__ __forceinline__ u64 shoup_mul(u64 y, u64 w, u64 ws, u64 nq) {
 }
 
 // Lazy Shoup product: y arbitrary 64-bit, w < q  ->  y*w mod q + {0,q,2q}  (< 3q).
-// The quotient estimate drops the yl*sl partial product (error <= 1), so the whole
-// multiply is 5 IMAD.WIDE + 4 IMAD -- 28 issue cycles of the 16-lane integer-multiply
-// pipe, which is the binding unit of the NTT on sm_100a (IMAD.WIDE occupies it for 4
-// cycles per warp, IMAD for 2: profiles/r1d_pipe_calibration.md).  Both cross terms use
-// mad.wide with a zero-extended 32-bit addend, which cannot overflow 64 bits, so no carry
-// chain is needed: s2 = yh*sl + lo32(yl*sh), k = yh*sh + hi32(yl*sh) + hi32(s2).
+// The quotient estimate drops only the yl*sl partial product: k = yh*sh + ((yl*sh + yh*sl) >> 32), with the 65-bit cross
+// sum kept exactly by a PTX carry chain (mad.lo.cc / madc.hi.cc).  ptxas turns the chain into
+//     IMAD.WIDE (yl*sh)  ->  IMAD.HI + carry-out (upper word of yh*sl + that)  ->  SEL (the carry as the pair's high word)
+//     ->  IMAD.WIDE (yh*sh + pair)
+// i.e. 2 IMAD.WIDE + 1 IMAD.HI + 1 SEL for the quotient and NO separate add: the whole butterfly is 4 IMAD.WIDE + 1 IMAD.HI
+// + 4 IMAD + 1 SEL + 4 IADD3 = 14 instructions (the r1 form, which passed zero-extended 32-bit addends to mad.wide, cost
+// 5 IMAD.WIDE + 4 IMAD + ~9 IADD3: ptxas splits such addends off into IADD3 pairs).  Multiplier-pipe cycles are about the
+// same (~27 against 28); issue slots and ALU work drop by a fifth (profiles/microbench/butterfly_fp64.cu V7).
+// Error: k_real - k in [0, 2)  =>  r = y*w - k*q in [0, 2q + q*y/2^64) < 3q for any 64-bit y.
 //
-// MODE 2 (NEAR: q = 2^bits - delta with delta < 2^31, the shape of every prime CoeffModulus::Create
-// hands out): 2^64 - q = (2^32 - 2^sh) 2^32 + delta with sh = bits - 32, so the kl * hi32(-q) term of
-// the remainder is just -(kl << sh): one multiplier-pipe IMAD becomes a shift on the ALU pipe.
+// MODE 2 (NEAR: q = 2^bits - delta with delta < 2^31, the shape of every prime CoeffModulus::Create hands out):
+// 2^64 - q = (2^32 - 2^sh) 2^32 + delta with sh = bits - 32, so the kl * hi32(-q) term of the remainder is just
+// -(kl << sh): one multiplier-pipe IMAD becomes a shift on the ALU pipe.
 template <int MODE = 1>
 __device__ __forceinline__ u64 shoup_mul_lazy(u64 y, u64 w, u64 ws, u64 nq, u32 nsh = 0) {
-    u32 yl, yh, wl, wh, sl, sh, nl, nh, c1l, c1h, kl, kh, rl, rh;
+    u32 yl, yh, wl, wh, sl, sh, nl, nh, kl, kh, rl, rh;
     unpack64(y, yl, yh);
     unpack64(w, wl, wh);
     unpack64(ws, sl, sh);
     unpack64(nq, nl, nh);
-    u64 c1, s2, k, r;
-    asm("mul.wide.u32 %0, %1, %2;" : "=l"(c1) : "r"(yl), "r"(sh));
-    unpack64(c1, c1l, c1h);
-    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(s2) : "r"(yh), "r"(sl), "l"((u64)c1l));
-    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(k) : "r"(yh), "r"(sh), "l"((u64)c1h));
-    k += (s2 >> 32);
-    unpack64(k, kl, kh);
+    u64 r;
+    asm("{\n\t.reg .u32 t0, t1, t2;\n\t"
+        "mul.lo.u32 t0, %2, %5;\n\t"             // lo(yl*sh)
+        "mul.hi.u32 t1, %2, %5;\n\t"             // hi(yl*sh)
+        "mad.lo.cc.u32 t0, %3, %4, t0;\n\t"      // + lo(yh*sl)
+        "madc.hi.cc.u32 t1, %3, %4, t1;\n\t"     // + hi(yh*sl) + carry
+        "addc.u32 t2, 0, 0;\n\t"                 // bit 64 of the cross sum
+        "mad.lo.cc.u32 %0, %3, %5, t1;\n\t"      // kl = lo(yh*sh) + t1
+        "madc.hi.u32 %1, %3, %5, t2;\n\t"        // kh = hi(yh*sh) + t2 + carry
+        "}" : "=r"(kl), "=r"(kh) : "r"(yl), "r"(yh), "r"(sl), "r"(sh));
     asm("mul.wide.u32 %0, %1, %2;" : "=l"(r) : "r"(yl), "r"(wl));
     asm("mad.wide.u32 %0, %1, %2, %0;" : "+l"(r) : "r"(kl), "r"(nl));
     unpack64(r, rl, rh);

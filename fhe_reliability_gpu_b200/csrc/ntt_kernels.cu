@@ -15,6 +15,8 @@
 #include "ntt_phases.cuh"
 #include "ctx.hpp"
 #include "abft.cuh"
+#include <atomic>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -63,8 +65,11 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 // ---------------------------------------------------------------- forward, columns
 // PROT: the protected transform (config C4) -- accumulates the input side of the
 // ABFT checksum while the coefficients are loaded and honours the injection plan.
+// resident CTAs per SM the column kernels are compiled for (register cap): 3 x 256 threads (85 registers); a cap of 4 (64
+// registers) spills and measured no faster; 512-row columns (LC = 9) fit 2
+__host__ __device__ constexpr int col_min_ctas(int LC, bool inverse) { return LC >= 9 ? 2 : 3; }
 template <int LC, int LA, int BIG, bool PROT, bool INJ>
-__global__ void __launch_bounds__(kTile * col_groups(LC, LA))
+__global__ void __launch_bounds__(kTile * col_groups(LC, LA), (PROT || INJ) ? 1 : col_min_ctas(LC, false))
 k_fwd_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
     static_assert(NG >= RB, "the first phase runs in one sweep");
@@ -132,32 +137,48 @@ k_fwd_col(PassArgs p) {
     }
 }
 
+// Lazy-range contract between the phases of the inverse transform (ntt_phases.cuh GsPlan): every phase reduces its
+// outputs that exceed kGsT q before handing them on, so the next phase (after the shared-memory exchange, or in the
+// column kernel after the trip through HBM) starts from a known bound instead of reducing everything again.
+constexpr int kGsT = 3;
+template <int BIG> __host__ __device__ constexpr int inv_row_b1() { return gs_out_bound<4, BIG, false, 0, kGsT>(); }              // after the row pass's first phase
+template <int BIG> __host__ __device__ constexpr int inv_row_b2() { return gs_out_bound<4, BIG, false, inv_row_b1<BIG>(), kGsT>(); }   // what the row pass stores
+
 // ---------------------------------------------------------------- row passes
-// One CTA = 16 rows of 256 coefficients of one limb, one row per half-warp, 16
-// coefficients per thread.  The 255 twiddles each row needs (x 16 rows = one
-// 64 KiB tile of the row table, laid out so that every shared-memory read is a
+// One CTA = kRowsPerCta (8) rows of 256 coefficients of one limb, one row per half-warp, 16
+// coefficients per thread.  The 255 twiddles each row needs (x 8 rows = one
+// 32 KiB tile of the row table, laid out so that every shared-memory read is a
 // conflict-free 128-bit access) arrive by ONE TMA bulk copy that overlaps the
 // coefficient loads; the two radix-16 register phases exchange through a
 // 16-byte-chunk XOR-swizzled shared tile.
-constexpr int kRowThreads = kRowsPerCta * 16;
+// NP polynomials that share the modulus (and so the twiddle tile) are processed side by side by one CTA (NP = 2 when the
+// batch has at least two): the 32 KiB tile is fetched once per NP x 16 KiB of coefficients instead of once per 16 KiB
+// (the row passes move twice as many twiddle bytes as data bytes through L2 otherwise), and the twiddle footprint per
+// warp halves, which lifts the shared-memory occupancy limit from 4 x 4 to 3 x 8 warps per SM.
+constexpr int kRowSlice = kRowsPerCta * 16;         // threads working on one polynomial's rows
+template <int NP>
 struct RowSmem {
     ulonglong2 twA[kRowsPerCta * 16];    // [row][15 + pad]: stages 0..3 of the row (broadcast reads)
-    ulonglong2 twB[15 * kRowThreads];    // [j][thread]:     stages 4..7, one list per thread
-    u64 x[kRowsPerCta * kRowLen];        // exchange tile
+    ulonglong2 twB[15 * kRowSlice];      // [j][thread]:     stages 4..7, one list per thread of a slice
+    u64 x[NP * kRowsPerCta * kRowLen];   // exchange tiles, one per polynomial
     u64 bar;
 };
 constexpr u32 kRowTileBytes = sizeof(ulonglong2) * kRowTileEntries;
-constexpr int kRowCtasPerSm = (220 * 1024) / (int)sizeof(RowSmem) > 16 ? 16 : (220 * 1024) / (int)sizeof(RowSmem);
+template <int NP> constexpr int row_ctas_per_sm() {
+    return (220 * 1024) / (int)sizeof(RowSmem<NP>) > 16 / NP ? 16 / NP : (220 * 1024) / (int)sizeof(RowSmem<NP>);
+}
 
-template <int BIG, bool PROT, bool INJ>
-__global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs p) {
+template <int BIG, bool PROT, bool INJ, int NP>
+__global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
-    RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
-    // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
-    // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
-    const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
+    RowSmem<NP>& s = *reinterpret_cast<RowSmem<NP>*>(smraw);
+    // grid: x = (tile, poly group) with the group fastest, y = limb of the polynomial.  CTAs that share a modulus (and
+    // so a twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other groups.
+    const u32 ng = p.n_poly / NP, grp = blockIdx.x % ng, tile = blockIdx.x / ng;
+    const int tslice = threadIdx.x % kRowSlice, pslot = threadIdx.x / kRowSlice;
+    const u32 poly = p.poly0 + grp * NP + pslot;
     const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
-    const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
+    const int cl = tslice & 15, rl = tslice >> 4;
 #ifndef B200_ABL_NOTMA
     if (threadIdx.x == 0) {
         mbar_init(&s.bar, 1);
@@ -183,7 +204,7 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
     if constexpr (INJ) ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m, Inject{p.inj, p.n_inj, p.limb0 + limb, x0 + cl, 4u, lc, m.q});
     else ct_phase<4, BIG>(v, TwList<1>{s.twA + rl * 16}, m);
     // exchange: thread cl holds positions e*16+cl, wants cl*16+e
-    unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + rl * (kRowLen * 8);
+    unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + (pslot * kRowsPerCta + rl) * (kRowLen * 8);
     {
         const u32 b0 = cl * 8;
 #pragma unroll
@@ -215,9 +236,9 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if constexpr (INJ)
-        ct_phase<4, BIG>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m, Inject{p.inj, p.n_inj, p.limb0 + limb, x0 + cl * 16, 0u, lc + 4, m.q});
+        ct_phase<4, BIG>(v, TwList<kRowSlice>{s.twB + tslice}, m, Inject{p.inj, p.n_inj, p.limb0 + limb, x0 + cl * 16, 0u, lc + 4, m.q});
     else
-        ct_phase<4, BIG>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m);
+        ct_phase<4, BIG>(v, TwList<kRowSlice>{s.twB + tslice}, m);
 #pragma unroll
     for (int e = 0; e < 16; e++) v[e] = BIG ? canon2(reduce_lazy<BIG>(v[e], m), m.q) : canon3(reduce_lazy<BIG>(v[e], m), m.q);
     ulonglong2* out = reinterpret_cast<ulonglong2*>(rowp + cl * 16);
@@ -240,19 +261,20 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_fwd_row(PassArgs
         }
         u64 s0, s1;
         acc.value(s0, s1);
-        abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1);
+        abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1, pslot, NP);
     }
 }
 
-template <int BIG>
-__global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs p) {
+template <int BIG, int NP>
+__global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
-    RowSmem& s = *reinterpret_cast<RowSmem*>(smraw);
-    // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
-    // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
-    const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
+    RowSmem<NP>& s = *reinterpret_cast<RowSmem<NP>*>(smraw);
+    // grid as in k_fwd_row: x = (tile, poly group) with the group fastest, y = limb
+    const u32 ng = p.n_poly / NP, grp = blockIdx.x % ng, tile = blockIdx.x / ng;
+    const int tslice = threadIdx.x % kRowSlice, pslot = threadIdx.x / kRowSlice;
+    const u32 poly = p.poly0 + grp * NP + pslot;
     const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
-    const int cl = threadIdx.x & 15, rl = threadIdx.x >> 4;
+    const int cl = tslice & 15, rl = tslice >> 4;
     if (threadIdx.x == 0) {
         mbar_init(&s.bar, 1);
         mbar_expect_tx(&s.bar, kRowTileBytes);
@@ -266,8 +288,8 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs
     for (int e = 0; e < 8; e++) { ulonglong2 x = in[e]; v[2 * e] = x.x; v[2 * e + 1] = x.y; }
     __syncthreads();
     mbar_wait(&s.bar, 0);
-    gs_phase<4, BIG, false>(v, TwList<kRowThreads>{s.twB + threadIdx.x}, m);
-    unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + rl * (kRowLen * 8);
+    gs_phase<4, BIG, false, 0, kGsT>(v, TwList<kRowSlice>{s.twB + tslice}, m);
+    unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + (pslot * kRowsPerCta + rl) * (kRowLen * 8);
     {
         const u32 a0 = cl * 128 + ((cl & 7) << 4);
 #pragma unroll
@@ -280,14 +302,14 @@ __global__ void __launch_bounds__(kRowThreads, kRowCtasPerSm) k_inv_row(PassArgs
 #pragma unroll
         for (int e = 0; e < 16; e++) v[e] = *reinterpret_cast<const u64*>(xrow + e * 128 + (b0 ^ ((e & 7) << 4)));
     }
-    gs_phase<4, BIG, false>(v, TwList<1>{s.twA + rl * 16}, m);
+    gs_phase<4, BIG, false, inv_row_b1<BIG>(), kGsT>(v, TwList<1>{s.twA + rl * 16}, m);
 #pragma unroll
     for (int e = 0; e < 16; e++) rowp[e * 16 + cl] = v[e];
 }
 
 // ---------------------------------------------------------------- inverse, columns
 template <int LC, int LA, int BIG>
-__global__ void __launch_bounds__(kTile * col_groups(LC, LA))
+__global__ void __launch_bounds__(kTile * col_groups(LC, LA), col_min_ctas(LC, true))
 k_inv_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
     static_assert(NG >= RB, "the last phase runs in one sweep");
@@ -312,7 +334,7 @@ k_inv_col(PassArgs p) {
             }
             __syncthreads();
             if (g < RA) {
-                gs_phase<LB, BIG, false>(w, TwShared{stw, (1u << LA) + g}, m);
+                gs_phase<LB, BIG, false, inv_row_b2<BIG>(), kGsT>(w, TwShared{stw, (1u << LA) + g}, m);
 #pragma unroll
                 for (int e = 0; e < RB; e++) sm[(g * RB + e) * kTile + c] = w[e];
             }
@@ -323,7 +345,7 @@ k_inv_col(PassArgs p) {
                 u64 w[RB];
 #pragma unroll
                 for (int e = 0; e < RB; e++) w[e] = base[(size_t)(gb * RB + e) * kRowLen + c];
-                gs_phase<LB, BIG, false>(w, TwShared{stw, (1u << LA) + gb}, m);
+                gs_phase<LB, BIG, false, inv_row_b2<BIG>(), kGsT>(w, TwShared{stw, (1u << LA) + gb}, m);
 #pragma unroll
                 for (int e = 0; e < RB; e++) sm[(gb * RB + e) * kTile + c] = w[e];
             }
@@ -339,7 +361,7 @@ k_inv_col(PassArgs p) {
 #pragma unroll
             for (int e = 0; e < RA; e++) v[e] = base[(size_t)(e * RB + g) * kRowLen + c];
         }
-        gs_phase<LA, BIG, true>(v, TwShared{stw, 1u}, m);
+        gs_phase<LA, BIG, true, (LB > 0 ? gs_out_bound<(LB > 0 ? LB : 1), BIG, false, inv_row_b2<BIG>(), kGsT>() : inv_row_b2<BIG>()), 0>(v, TwShared{stw, 1u}, m);
 #pragma unroll
         for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
     }
@@ -428,44 +450,95 @@ __global__ void k_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 s
 }
 
 // ---------------------------------------------------------------- dispatch
+// cudaFuncAttributeMaxDynamicSharedMemorySize is set once per kernel instantiation (not on every launch), and checked
+// (the kernel is a non-type template argument: one static per instantiation, not per function-pointer TYPE)
+// and per device: the attribute belongs to the device's context)
+template <auto Kernel>
+static cudaError_t set_smem_once(size_t smem) {
+    static std::atomic<unsigned long long> done{0};
+    if (smem <= 48 * 1024) return cudaSuccess;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_relaxed) & bit) return cudaSuccess;
+    const cudaError_t rc = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (rc == cudaSuccess) done.fetch_or(bit, std::memory_order_relaxed);
+    return rc;
+}
+// row passes: pairs of polynomials share a CTA (and its twiddle tile); an odd last polynomial runs the one-poly form
+// Measured on B200 (profiles/r2e_ablations.txt): the paired form is NOT faster (fwd 107 vs 99 us, inv 103 vs 98.5 us per 288-limb
+// batch) -- the row passes are bound by their own instruction stream, not by twiddle traffic or occupancy -- so it stays an
+// option (B200FHE_ROW_NP=2) and the one-polynomial form is the default.
+static const bool g_row_pairs = getenv("B200FHE_ROW_NP") && atoi(getenv("B200FHE_ROW_NP")) == 2;
+template <int BIG, bool PROT, bool INJ>
+static int launch_fwd_row(PassArgs a, u32 np, cudaStream_t s) {
+    const u32 tiles = (a.N >> kRowLog) / kRowsPerCta, pairs = g_row_pairs ? np / 2 : 0;
+    if (pairs) {
+        if (set_smem_once<k_fwd_row<BIG, PROT, INJ, 2>>(sizeof(RowSmem<2>)) != cudaSuccess) return -4;
+        a.n_poly = pairs * 2; a.poly0 = 0;
+        k_fwd_row<BIG, PROT, INJ, 2><<<dim3(tiles * pairs, a.L), kRowSlice * 2, sizeof(RowSmem<2>), s>>>(a);
+    }
+    if (np - 2 * pairs) {
+        if (set_smem_once<k_fwd_row<BIG, PROT, INJ, 1>>(sizeof(RowSmem<1>)) != cudaSuccess) return -4;
+        a.n_poly = np - 2 * pairs; a.poly0 = 2 * pairs;
+        k_fwd_row<BIG, PROT, INJ, 1><<<dim3(tiles * a.n_poly, a.L), kRowSlice, sizeof(RowSmem<1>), s>>>(a);
+    }
+    return 0;
+}
+template <int BIG>
+static int launch_inv_row(PassArgs a, u32 np, cudaStream_t s) {
+    const u32 tiles = (a.N >> kRowLog) / kRowsPerCta, pairs = g_row_pairs ? np / 2 : 0;
+    if (pairs) {
+        if (set_smem_once<k_inv_row<BIG, 2>>(sizeof(RowSmem<2>)) != cudaSuccess) return -4;
+        a.n_poly = pairs * 2; a.poly0 = 0;
+        k_inv_row<BIG, 2><<<dim3(tiles * pairs, a.L), kRowSlice * 2, sizeof(RowSmem<2>), s>>>(a);
+    }
+    if (np - 2 * pairs) {
+        if (set_smem_once<k_inv_row<BIG, 1>>(sizeof(RowSmem<1>)) != cudaSuccess) return -4;
+        a.n_poly = np - 2 * pairs; a.poly0 = 2 * pairs;
+        k_inv_row<BIG, 1><<<dim3(tiles * a.n_poly, a.L), kRowSlice, sizeof(RowSmem<1>), s>>>(a);
+    }
+    return 0;
+}
 template <int LC, int LA, int BIG, bool PROT = false, bool INJ = false>
-static void launch_fwd2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
+static int launch_fwd2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
     const u32 np = n_limbs / a_in.L;
     PassArgs a = a_in;
     a.n_poly = np;
-    dim3 gc((kRowLen / kTile) * np, a.L), gr(((a.N >> kRowLog) / kRowsPerCta) * np, a.L);
+    dim3 gc((kRowLen / kTile) * np, a.L);
     constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_fwd_col<LC, LA, BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (mask & 1) k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
-    if (mask & 2) {
-        cudaFuncSetAttribute(k_fwd_row<BIG, PROT, INJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
-        k_fwd_row<BIG, PROT, INJ><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
+    if (mask & 1) {
+        if (set_smem_once<k_fwd_col<LC, LA, BIG, PROT, INJ>>(smem) != cudaSuccess) return -4;
+        k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
     }
+    if (mask & 2) return launch_fwd_row<BIG, PROT, INJ>(a, np, s);
+    return 0;
 }
 template <int LC, int LA, int BIG>
-static void launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
+static int launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
     const u32 np = n_limbs / a_in.L;
     PassArgs a = a_in;
     a.n_poly = np;
-    dim3 gc((kRowLen / kTile) * np, a.L), gr(((a.N >> kRowLog) / kRowsPerCta) * np, a.L);
+    dim3 gc((kRowLen / kTile) * np, a.L);
     if (mask & 1) {
-        cudaFuncSetAttribute(k_inv_row<BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowSmem));
-        k_inv_row<BIG><<<gr, kRowThreads, sizeof(RowSmem), s>>>(a);
+        int rc = launch_inv_row<BIG>(a, np, s);
+        if (rc) return rc;
     }
     constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_inv_col<LC, LA, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (mask & 2) k_inv_col<LC, LA, BIG><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
+    if (mask & 2) {
+        if (set_smem_once<k_inv_col<LC, LA, BIG>>(smem) != cudaSuccess) return -4;
+        k_inv_col<LC, LA, BIG><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
+    }
+    return 0;
 }
 
 template <int BIG>
 static int launch_ntt_t(bool inverse, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
 #define B200_CASE(LOGN, LC, LA)                                              \
     case LOGN:                                                               \
-        if (inverse) launch_inv2<LC, LA, BIG>(a, n_limbs, mask, s);                \
-        else launch_fwd2<LC, LA, BIG>(a, n_limbs, mask, s);                        \
-        return 0;
+        return inverse ? launch_inv2<LC, LA, BIG>(a, n_limbs, mask, s) : launch_fwd2<LC, LA, BIG>(a, n_limbs, mask, s);
     switch (logn) {
 #ifndef B200_FAST_BUILD      // experiment builds instantiate the N = 2^16 kernels only
         B200_CASE(12, 4, 4)
@@ -490,14 +563,15 @@ int launch_ntt(bool inverse, int big, const PassArgs& a, int logn, u32 n_limbs, 
         else k_small<false, false><<<n_limbs, 256, smem, s>>>(a, logn);
         return 0;
     }
-    // grid.y limit is 65535 limbs per launch: split long batches
-    const u32 kMaxY = 32768;
-    for (u32 off = 0; off < n_limbs; off += kMaxY) {
+    // n_limbs = n_poly * L whole polynomials (limb l of each uses modulus start_mod + l); grid.y = L, grid.x = tiles * n_poly
+    // is far below its 2^31 - 1 limit, so the only split is a safety bound of 32768 limbs per launch, cut at polynomial
+    // boundaries so the limb -> modulus mapping is kept
+    if (a.L == 0 || n_limbs % a.L) return -2;
+    const u32 kMaxLimbs = (32768 / a.L ? 32768 / a.L : 1) * a.L;
+    for (u32 off = 0; off < n_limbs; off += kMaxLimbs) {
         PassArgs b = a;
         b.data = a.data + (size_t)off * a.N;
-        // keep limb->modulus mapping: off must be a multiple of L
-        u32 cnt = n_limbs - off < kMaxY ? n_limbs - off : kMaxY;
-        if (off % a.L) return -2;
+        u32 cnt = n_limbs - off < kMaxLimbs ? n_limbs - off : kMaxLimbs;
 #ifdef B200_FAST_BUILD
         int rc = big == 2 ? launch_ntt_t<2>(inverse, b, logn, cnt, mask, s) : big ? launch_ntt_t<1>(inverse, b, logn, cnt, mask, s) : -3;
 #else
@@ -513,20 +587,20 @@ template <int BIG, bool INJ>
 static int launch_prot_t(const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
     switch (logn) {
 #ifndef B200_FAST_BUILD
-        case 12: launch_fwd2<4, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
-        case 13: launch_fwd2<5, 3, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
-        case 14: launch_fwd2<6, 3, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
-        case 15: launch_fwd2<7, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
-        case 17: launch_fwd2<9, 5, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 12: return launch_fwd2<4, 4, BIG, true, INJ>(a, n_limbs, 3, s);
+        case 13: return launch_fwd2<5, 3, BIG, true, INJ>(a, n_limbs, 3, s);
+        case 14: return launch_fwd2<6, 3, BIG, true, INJ>(a, n_limbs, 3, s);
+        case 15: return launch_fwd2<7, 4, BIG, true, INJ>(a, n_limbs, 3, s);
+        case 17: return launch_fwd2<9, 5, BIG, true, INJ>(a, n_limbs, 3, s);
 #endif
-        case 16: launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, 3, s); return 0;
+        case 16: return launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, 3, s);
     }
     return -1;
 }
 
 int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
     if (n_limbs == 0) return 0;
-    if (n_limbs > 32768) return -2;
+    if (n_limbs > 32768 || a.L == 0 || n_limbs % a.L) return -2;
     if (logn >= 1 && logn <= 11) {
         k_small<false, true><<<n_limbs, 256, sizeof(u64) << logn, s>>>(a, logn);
         return 0;

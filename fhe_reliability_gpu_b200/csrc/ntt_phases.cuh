@@ -114,33 +114,84 @@ __device__ __forceinline__ void ct_phase(u64 (&v)[1 << LR], const TW& tw, const 
     }
 }
 
-// Inverse Gentleman-Sande phase.  In: any 64-bit words.  Out: lazily reduced
-// values (< 16q) unless LAST, in which case the final sub-stage (global stage 0)
-// folds N^-1 in and the outputs are canonical [0,q).
-template <int LR, int BIG, bool LAST, class TW>
+// ---- lazy-range plan of a Gentleman-Sande phase (compile time) -----------------------------------------------------
+// Values ride as multiples of q below 16q (q < 2^60).  A GS butterfly (U, V) -> (U + V, (U - V + c q) w) needs
+// bound(U) + bound(V) <= 16 and bound(U) + c <= 16 with c q >= V; products come back below 3q, sums add their bounds.
+// The r1 code tracked ONE worst-case bound for all elements and re-reduced half the vector when it passed 8: 24
+// reductions per radix-16 phase.  Tracking the bound of every element (the butterfly network is fixed, so this is pure
+// compile-time bookkeeping) shows that only the few elements on an all-sums path ever get close to 16q: 19 reductions
+// when the inputs are unknown words (16 of them the input reduction itself), 3-9 when the producer guarantees a bound.
+// IN_B: bound of every input in units of q (0: arbitrary 64-bit words -> all are reduced first).
+// OUT_T: outputs whose bound exceeds OUT_T are reduced at the end (0: leave them), so the consumer can start from OUT_T.
+struct GsPlan {
+    unsigned red[6];             // [n]: elements reduced before sub-stage n (bit e); [LR]: reduced at the end
+    unsigned char c[5][16];      // [n][butterfly]: multiple of q added to U - V
+    unsigned char out[32];       // output bounds (after the end reductions)
+    unsigned char out_max;
+};
+__host__ __device__ constexpr int gs_const_ge(int b) {
+    const int cs[8] = {1, 2, 3, 4, 6, 8, 12, 16};
+    for (int i = 0; i < 8; i++)
+        if (cs[i] >= b) return cs[i];
+    return 0;
+}
+template <int LR, int LAZYB, int IN_B, int OUT_T, bool LAST>
+__host__ __device__ constexpr GsPlan gs_make_plan() {
+    constexpr int R = 1 << LR;
+    GsPlan p{};
+    int bnd[32] = {};
+    for (int e = 0; e < R; e++) bnd[e] = IN_B ? IN_B : LAZYB;
+    if (!IN_B) p.red[0] = R == 32 ? 0xffffffffu : ((1u << R) - 1u);
+    for (int n = 0; n < LR; n++) {
+        const int t = LR - 1 - n, half = R >> (t + 1);
+        int bf = 0;
+        for (int g = 0; g < (1 << t); g++)
+            for (int i = 0; i < half; i++, bf++) {
+                const int a = g * 2 * half + i, b = a + half;
+                int ba = bnd[a], bb = bnd[b], c = gs_const_ge(bb);
+                if (!(ba + bb <= 16 && c && ba + c <= 16)) {
+                    // cheapest fix first: V alone, U alone, both
+                    const int cb = gs_const_ge(LAZYB);
+                    if (ba + LAZYB <= 16 && ba + cb <= 16) { p.red[n] |= 1u << b; bb = LAZYB; }
+                    else if (LAZYB + bb <= 16 && c && LAZYB + c <= 16) { p.red[n] |= 1u << a; ba = LAZYB; }
+                    else { p.red[n] |= (1u << a) | (1u << b); ba = bb = LAZYB; }
+                    c = gs_const_ge(bb);
+                }
+                p.c[n][bf] = (unsigned char)c;
+                bnd[a] = (LAST && t == 0) ? 3 : ba + bb;
+                bnd[b] = 3;
+            }
+    }
+    for (int e = 0; e < R; e++) {
+        if (OUT_T && bnd[e] > OUT_T) { p.red[LR] |= 1u << e; bnd[e] = LAZYB; }
+        p.out[e] = (unsigned char)bnd[e];
+        if (bnd[e] > p.out_max) p.out_max = (unsigned char)bnd[e];
+    }
+    return p;
+}
+
+// Inverse Gentleman-Sande phase.  In: words below IN_B q (IN_B = 0: any 64-bit words).  Out: lazily reduced values
+// below gs_out_bound<...>() q unless LAST, in which case the final sub-stage (global stage 0) folds N^-1 in and the
+// outputs are canonical [0,q).
+template <int LR, int BIG, bool LAST, int IN_B, int OUT_T>
+__host__ __device__ constexpr int gs_out_bound() { return gs_make_plan<LR, LazyBound<BIG>::value, IN_B, OUT_T, LAST>().out_max; }
+
+template <int LR, int BIG, bool LAST, int IN_B = 0, int OUT_T = 0, class TW>
 __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const B200Mod& m) {
     constexpr int R = 1 << LR;
 #ifdef B200_ABL_NOCOMPUTE
     if (m.q != 12345) return;
 #endif
+    constexpr GsPlan P = gs_make_plan<LR, LazyBound<BIG>::value, IN_B, OUT_T, LAST>();
     const u64 q = m.q, nq = 0 - q;
     const u32 sh = m.bits - 32;            // NEAR only
-#pragma unroll
-    for (int e = 0; e < R; e++) v[e] = reduce_lazy<BIG>(v[e], m);
-    int bound = LazyBound<BIG>::value;                                  // compile-time after unroll
 #pragma unroll
     for (int n = 0; n < LR; n++) {
         const int t = LR - 1 - n;
         const int half = R >> (t + 1);
-        if (bound > 8) {                       // sums would pass 16q: re-reduce the big (sum) elements
-            const int phalf = half >> 1;       // previous sub-stage's half
 #pragma unroll
-            for (int e = 0; e < R; e++)
-                if ((e & phalf) == 0) v[e] = reduce_lazy<BIG>(v[e], m);
-            bound = 3;                         // the product elements stay below 3q
-        }
-        // bound is 2^k or 3*2^k: shifts of q or of the memory-resident 3q (no multiplier-pipe rematerialisation)
-        const u64 bq = (bound % 3 == 0) ? (m.q3 << (31 - __builtin_clz(bound / 3))) : (q << (31 - __builtin_clz(bound)));
+        for (int e = 0; e < R; e++)
+            if ((P.red[n] >> e) & 1u) v[e] = reduce_lazy<BIG>(v[e], m);
         const bool fold = LAST && (t == 0);
 #pragma unroll
         for (int g = 0; g < (1 << t); g++) {
@@ -150,16 +201,19 @@ __device__ __forceinline__ void gs_phase(u64 (&v)[1 << LR], const TW& tw, const 
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int a = g * 2 * half + i, b = a + half;
+                // c q with c in {1,2,3,4,6,8,12,16}: shifts of q or of the memory-resident 3q (no multiplier-pipe rematerialisation)
+                const int c = P.c[n][g * half + i];
+                const u64 bq = (c % 3 == 0) ? (m.q3 << (31 - __builtin_clz(c / 3))) : (q << (31 - __builtin_clz(c)));
                 const u64 U = v[a], V = v[b];
                 const u64 S = U + V;
                 v[b] = shoup_mul_lazy<BIG>(U - V + bq, W.x, W.y, nq, sh);
                 v[a] = fold ? shoup_mul_lazy<BIG>(S, m.ninv, m.ninv_s, nq, sh) : S;
             }
         }
-        bound *= 2;
     }
-    if (LAST) {
 #pragma unroll
-        for (int e = 0; e < R; e++) v[e] = canon3(v[e], q);
+    for (int e = 0; e < R; e++) {
+        if ((P.red[LR] >> e) & 1u) v[e] = reduce_lazy<BIG>(v[e], m);
+        if (LAST) v[e] = canon3(v[e], q);
     }
 }

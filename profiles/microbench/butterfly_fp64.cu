@@ -3,6 +3,8 @@
 //
 //   V2  the r1 product: k = yh sh + hi32(yl sh) + hi32(yh sl + lo32(yl sh))      5 IMAD.WIDE + 4 IMAD, r < 3q
 //   V3  integer, cheaper estimate: k = yh sh + hi32(yl sh) + hi32(yh sl)         3 IMAD.WIDE + 2 IMAD.HI + 4 IMAD, r < 4q
+//   V7  integer, the cross sum kept exactly by a PTX carry chain (mad.lo.cc / madc.hi.cc): ptxas emits IMAD.WIDE, IMAD.HI with
+//       carry-out, SEL, IMAD.WIDE and no separate adds                             4 IMAD.WIDE + 1 IMAD.HI + 4 IMAD + 1 SEL, r < 3q
 //   V6  FP64 estimate: k = yh sh + int(fma(Yl, a, fma(Yh, b, C)))                3 IMAD.WIDE + 4 IMAD + 2 DFMA,    r < 4q
 //
 // V6: k = floor(y ws / 2^64) = yh sh + (yl sh + yh sl) / 2^32 + (< 1).  The middle term S is < 2^33 and only its integer part
@@ -48,6 +50,17 @@ __device__ __forceinline__ void bf_int(u64& X, u64& Y, const TwRaw& t, const Mod
         asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(s2) : "r"(yh), "r"(sl), "l"((u64)c1l));
         asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(k) : "r"(yh), "r"(sh), "l"((u64)c1h));
         k += (s2 >> 32);
+    } else if (V == 7) {   // carry chain: k = yh sh + ((yl sh + yh sl) >> 32) exactly; ptxas: WIDE, IMAD.HI + carry-out, SEL, WIDE
+        asm("{\n\t.reg .u32 t0, t1, t2;\n\t"
+            "mul.lo.u32 t0, %2, %5;\n\t"
+            "mul.hi.u32 t1, %2, %5;\n\t"
+            "mad.lo.cc.u32 t0, %3, %4, t0;\n\t"
+            "madc.hi.cc.u32 t1, %3, %4, t1;\n\t"
+            "addc.u32 t2, 0, 0;\n\t"
+            "mad.lo.cc.u32 %0, %3, %5, t1;\n\t"
+            "madc.hi.u32 %1, %3, %5, t2;\n\t"
+            "}" : "=r"(kl), "=r"(kh) : "r"(yl), "r"(yh), "r"(sl), "r"(sh));
+        k = pack64(kl, kh);
     } else {
         u32 h1, h2;
         asm("mul.hi.u32 %0, %1, %2;" : "=r"(h1) : "r"(yl), "r"(sh));
@@ -65,7 +78,7 @@ __device__ __forceinline__ void bf_int(u64& X, u64& Y, const TwRaw& t, const Mod
     asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(rh) : "r"(kh), "r"(nl));
     const u64 T = pack64(rl, rh), x = X;
     X = x + T;
-    Y = x - T + (V == 2 ? m.q3 : m.q4);            // V3: k_est in (k_real - 3, k_real] -> r < 3q + q y / 2^64 < 4q
+    Y = x - T + (V == 2 || V == 7 ? m.q3 : m.q4);            // V3: k_est in (k_real - 3, k_real] -> r < 3q + q y / 2^64 < 4q
 }
 __device__ __forceinline__ u64 reduce_near(u64 v, const ModC& m) {   // any v -> < 2q: one IMAD.WIDE
     u32 vl, vh;
@@ -160,7 +173,7 @@ __global__ void __launch_bounds__(256, V == 6 ? 1 : 2) k(u64* out, const ModC* m
 #pragma unroll
         for (int t = 0; t < 4; t++) {
             const int half = 8 >> t;
-            if (V != 2 && t == 3) {          // products < 4q: X path 2 + 3*4 = 14q, one more sub-stage would pass 16q
+            if (V != 2 && V != 7 && t == 3) {          // products < 4q: X path 2 + 3*4 = 14q, one more sub-stage would pass 16q
 #pragma unroll
                 for (int e = 0; e < 16; e += 2) { if (V == 6) reduce_near(c[e], m); else v[e] = reduce_near(v[e], m); }
             }
@@ -279,6 +292,8 @@ int main() {
     cudaMalloc(&d_m, sizeof(ModC));
     cudaMemcpy(d_m, &m, sizeof(ModC), cudaMemcpyHostToDevice);
     run<2, 0>("V2 int 5W+4I, CTA-shared twiddles", d_tw, h_tw, d_m, q);
+    run<7, 0>("V7 int carry chain 4W+1HI+4I, CTA-shared", d_tw, h_tw, d_m, q);
+    run<7, 1>("V7 int carry chain 4W+1HI+4I, per-thread", d_tw, h_tw, d_m, q);
     run<3, 0>("V3 int 3W+2HI+4I, CTA-shared twiddles", d_tw, h_tw, d_m, q);
     run<6, 0>("V6 fp64 3W+4I+2DFMA, CTA-shared prepared", d_tw, h_tw, d_m, q);
     run<2, 1>("V2 int 5W+4I, per-thread twiddles", d_tw, h_tw, d_m, q);
