@@ -320,6 +320,8 @@ def main():
         torch.cuda.empty_cache()
         sub["pmult"] = bench_sub.pmult_record(pkg, torch, O, peak, local, check=not NOCHECK)
         sub["modup"], sub["keyswitch"] = bench_sub.keyswitch_records(pkg, torch, O, peak, local, check=not NOCHECK)
+        torch.cuda.empty_cache()
+        sub["fold_check"] = bench_sub.fold_record(pkg, torch, O, peak, local, check=not NOCHECK)
         if world > 1:
             barrier()
 

@@ -66,6 +66,9 @@ SIGNATURES = {
     "b200fhe_poly_add": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "b200fhe_poly_sub": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "b200fhe_galois_ntt": (i32, [vp, vp, vp, C.c_uint32, sz, vp]),
+    "b200fhe_barrett_params": (i32, [u64, C.POINTER(i32), U64P]),
+    "b200fhe_barrett_fold": (i32, [u64, vp, vp, vp, sz, sz, i32, i32, i32, i32, vp, sz, vp, vp, vp, vp]),
+    "b200fhe_barrett_fold_host": (i32, [u64, U64P, U64P, U64P, sz, sz, i32, i32, i32, i32, vp, sz, U64P, U64P, C.POINTER(C.c_uint32), i32]),
     "b200fhe_flip_bit": (i32, [vp, sz, C.c_uint, vp]),
     "b200fhe_host_alloc": (i32, [C.POINTER(vp), sz]),
     "b200fhe_host_free": (i32, [vp]),
@@ -420,3 +423,40 @@ def relia_four_step_host(q, g, a, weights, faults=(), fold_bits=4, want_out=True
     check(lib().b200fhe_relia_four_step_host(q, g, N, fold_bits, _p(a), _p(out) if want_out else None, _p(weights), trials,
                                              C.cast(arr, vp), nf, flags.ctypes.data_as(C.POINTER(C.c_uint32)), device))
     return out, flags
+
+
+class FoldFault(C.Structure):
+    """b200fhe_fold_fault: a fault at one of the Barrett multiplier's two product outputs (barrett_final.cpp:6-7)."""
+    _fields_ = [("index", C.c_uint64), ("payload", C.c_uint64), ("product", C.c_uint32), ("kind", C.c_uint32)]
+
+
+def barrett_params(q):
+    K, mu = i32(), u64()
+    check(lib().b200fhe_barrett_params(q, C.byref(K), C.byref(mu)))
+    return int(K.value), int(mu.value)
+
+
+def barrett_fold_host(q, a, b, fold, k=None, faults=(), propagate=0, device=0):
+    """f4: element-wise Barrett products of a, b [n_vec][vec_len] on the device with the per-group XOR signatures
+    (barrett_final.cpp "instra" / "sum") and, when k is given, the mod 2^k + 1 residue verdicts (outer_check.cpp
+    "intra" bit 0 / "inter" bit 1, subtractor bit 2).  faults: (index, product, kind, payload) or a FoldFault array.
+    Returns (c, sig_intra, sig_sum, verdict or None)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64); b = np.ascontiguousarray(b, dtype=np.uint64)
+    n_vec, vec_len = a.shape
+    groups = n_vec * ((vec_len + fold - 1) // fold)
+    c = np.zeros_like(a)
+    s1, s2 = np.zeros(groups, dtype=np.uint64), np.zeros(groups, dtype=np.uint64)
+    v = np.zeros(groups, dtype=np.uint32)
+    if isinstance(faults, np.ndarray):
+        assert faults.dtype.itemsize == C.sizeof(FoldFault) and faults.flags.c_contiguous
+        arr, nf = faults.ctypes.data_as(vp), len(faults)
+    else:
+        faults = list(faults)
+        nf = len(faults)
+        arr = (FoldFault * max(nf, 1))()
+        for i, (idx, prod, kind, payload) in enumerate(faults):
+            arr[i] = FoldFault(int(idx), int(payload), int(prod), int(kind))
+        arr = C.cast(arr, vp)
+    check(lib().b200fhe_barrett_fold_host(q, _p(a), _p(b), _p(c), n_vec, vec_len, fold, k or 0, 1 if k else 0, propagate, arr, nf,
+                                          _p(s1), _p(s2), v.ctypes.data_as(C.POINTER(C.c_uint32)), device))
+    return c, s1, s2, (v if k else None)

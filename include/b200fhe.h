@@ -336,6 +336,39 @@ int b200fhe_poly_sub(b200fhe_ctx* ctx, uint64_t* d_a, const uint64_t* d_b, size_
  * (modulus-independent), galois_elt odd in [1, 2N); out of place. */
 int b200fhe_galois_ntt(b200fhe_ctx* ctx, const uint64_t* d_in, uint64_t* d_out, uint32_t galois_elt, size_t n_limbs, void* stream);
 
+/* ---- intra-multiplier fold checks of the Barrett multiplier ------------------------
+ * rfhe_framewk/src/barrett_final.cpp:120-141 (barrett_reduce_signatures: c, lowK(mul1), lowK(mul2) of one Barrett
+ * reduction, K = bit_length(q-1), mu = floor(2^2K/q)) and :175-266 (XOR of the signatures over fold groups, compared
+ * between two executions), and the mod 2^k + 1 residue fold of rfhe_framewk/src/barrett_test/outer_check.cpp:35-50
+ * with its per-element ("intra") and per-vector ("inter") comparisons (:222-252). */
+typedef struct b200fhe_fold_fault {
+    uint64_t index;      /* element, vec * vec_len + i */
+    uint64_t payload;    /* XOR mask (kind 1) or replacement value (kind 2), taken inside the low K bits */
+    uint32_t product;    /* 1: mul1 = t * mu, 2: mul2 = s * q  (barrett_final.cpp:6-7: faults at multiplication outputs) */
+    uint32_t kind;       /* 1: SBF / DBF (flip_k_limited :97-115), 2: MOF (rand_sig :116-120) */
+} b200fhe_fold_fault;
+
+/* make_barrett_ctx (barrett_final.cpp:74-80). */
+int b200fhe_barrett_params(uint64_t q, int* K, uint64_t* mu);
+
+/* c[v][i] = Barrett(a[v][i] * b[v][i]) exactly as barrett_reduce_signatures computes it (t = low 64 bits of a b, so a
+ * true modular product for q < 2^32), for n_vec vectors of vec_len elements, with, per group of `fold` consecutive
+ * elements of a vector (ceil(vec_len / fold) groups per vector, the last one short as at barrett_final.cpp:262-264):
+ *   d_sig_intra[g] = XOR_i lowK(mul1_i) ^ lowK(mul2_i)     ("instra", :251-253)
+ *   d_sig_sum[g]   = XOR_i lowK(c_i)                       ("sum",    :254-257)
+ * and, when mode bit 0 is set, d_verdict[g]: bit 0 = some element failed the residue check of its products
+ * R(mul1) == R(t) R(mu), R(mul2) == R(s) R(q) mod 2^k + 1 (outer_check.cpp "intra"), bit 1 = the group's summed
+ * predicted and observed residues differ ("inter"), bit 2 = the subtraction t - mul2 failed its residue identity.
+ * mode -1 runs the plain unchecked product (overhead baseline).  propagate = 0: faults touch only what the checks see
+ * (the reference's signature-domain model, barrett_final.cpp:9); 1: the corrupted product is used by the arithmetic.
+ * 2 <= k <= 26.  Faults live in host memory. */
+int b200fhe_barrett_fold(uint64_t q, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_c, size_t n_vec, size_t vec_len,
+                         int fold, int k, int mode, int propagate, const b200fhe_fold_fault* h_faults, size_t n_faults,
+                         uint64_t* d_sig_intra, uint64_t* d_sig_sum, uint32_t* d_verdict, void* stream);
+int b200fhe_barrett_fold_host(uint64_t q, const uint64_t* h_a, const uint64_t* h_b, uint64_t* h_c, size_t n_vec, size_t vec_len,
+                              int fold, int k, int mode, int propagate, const b200fhe_fold_fault* h_faults, size_t n_faults,
+                              uint64_t* h_sig_intra, uint64_t* h_sig_sum, uint32_t* h_verdict, int device);
+
 /* Measurement hooks (bench.py): one pass of the two-kernel transform
  * (pass 1 = first kernel, 2 = second), and the number of kernels this library
  * has launched in this process. */

@@ -89,6 +89,9 @@ def lib():
             ("orc_cyclic_ntt_radix2", None, [U64P, u64, u64, u64]),
             ("orc_four_step_cyclic", i32, [U64P, U64P, u64, u64, u64, U64P, U64P]),
             ("orc_protection_check_blockdiag", i32, [U64P, U64P, u64, u64, u64, u64, U64P, U64P]),
+            ("orc_barrett_params", i32, [u64, C.POINTER(i32), U64P]),
+            ("orc_fold_residue", C.c_uint32, [u64, u64, i32]),
+            ("orc_barrett_fold", None, [u64, U64P, U64P, U64P, u64, u64, i32, i32, i32, C.c_void_p, i32, U64P, U64P, C.c_void_p]),
         ]:
             f = getattr(L, name)
             f.restype, f.argtypes = res, args
@@ -448,3 +451,32 @@ def bconv_exact(x, p, qo):
         for k, q in enumerate(qo):
             out[k, i] = v % int(q)
     return out
+
+
+class _FoldFault(C.Structure):
+    _fields_ = [("index", C.c_uint64), ("payload", C.c_uint64), ("product", C.c_uint32), ("kind", C.c_uint32)]
+
+
+def barrett_params(q):
+    """make_barrett_ctx (barrett_final.cpp:74-80): (K, mu)."""
+    K, mu = C.c_int(), C.c_uint64()
+    lib().orc_barrett_params(q, C.byref(K), C.byref(mu))
+    return int(K.value), int(mu.value)
+
+
+def barrett_fold(q, a, b, fold, k=None, faults=(), propagate=0):
+    """Element-wise Barrett products of a, b [n_vec][vec_len] with the group signatures / residue verdicts of f4.
+    faults: (index, product, kind, payload).  Returns (c, sig_intra, sig_sum, verdict or None)."""
+    a = np.ascontiguousarray(a, dtype=np.uint64); b = np.ascontiguousarray(b, dtype=np.uint64)
+    n_vec, vec_len = a.shape
+    groups = n_vec * ((vec_len + fold - 1) // fold)
+    c = np.zeros_like(a)
+    s1, s2 = np.zeros(groups, dtype=np.uint64), np.zeros(groups, dtype=np.uint64)
+    v = np.zeros(groups, dtype=np.uint32) if k else None
+    faults = list(faults)
+    arr = (_FoldFault * max(len(faults), 1))()
+    for i, (idx, prod, kind, payload) in enumerate(faults):
+        arr[i] = _FoldFault(int(idx), int(payload), int(prod), int(kind))
+    lib().orc_barrett_fold(q, _p(a), _p(b), _p(c), n_vec, vec_len, fold, k or 0, propagate, C.cast(arr, C.c_void_p), len(faults),
+                           _p(s1), _p(s2), v.ctypes.data_as(C.c_void_p) if k else None)
+    return c, s1, s2, v
