@@ -323,6 +323,8 @@ def main():
         torch.cuda.empty_cache()
         sub["fold_check"] = bench_sub.fold_record(pkg, torch, O, peak, local, check=not NOCHECK)
         if world > 1:
+            torch.cuda.empty_cache()
+            sub["modup_sharded"] = bench_sub.modup_sharded_record(pkg, torch, dist, rank, world, local, peak)
             barrier()
 
     if rank == 0:

@@ -33,7 +33,7 @@ def _graphed(torch, fn):
             fn()
         torch.cuda.current_stream().wait_stream(side)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):      # NCCL's helper threads may call CUDA while we capture
             fn()
         return g.replay
     except Exception:
@@ -174,3 +174,77 @@ def fold_record(pkg, torch, O, peak, device, steps=10, check=True):
             "roofline": {"bound": "hbm", "achieved": algo / (ms_plain * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": algo / (ms_plain * 1e-3) / 1e9 / peak,
                          "algorithmic_bytes_per_call": algo, "note": "plain product; the checked variants move the same bytes + 20 B per group"},
             "parity_vs_oracle": parity, "parity_scope": "64 vectors: products, both signatures, zero verdicts, bit-exact"}
+
+
+def modup_sharded_record(pkg, torch, dist, rank, world, local, peak, log_n=17, n_q=48, n_p=16, dnum=3, steps=20, warmup=3, graph=True):
+    """C5 through the C ABI's limb-sharded ModUp (b200fhe_modup_sharded: one NCCL all-gather per digit on the plan's
+    communication stream, overlapped with the previous digit's contraction + NTT).  Every rank first checks its owned
+    output limbs bit for bit against the UNSHARDED b200fhe_keyswitch_modup run on its own GPU; timing = CUDA events on
+    the launching stream, barrier on both sides, max over ranks.  Returns the record on every rank."""
+    B = pkg.binding
+    N, total, alpha = 1 << log_n, n_q + n_p, n_q // dnum
+    moduli = pkg.primes_create(N, [60] * total)
+    rng = np.random.default_rng(20250606)                                  # identical on every rank
+    c = np.stack([rng.integers(0, q, size=N, dtype=np.uint64) for q in moduli[:n_q]])
+    shard = B.Shard(rank, world, local, dist if world > 1 else None)
+    plan = B.ModUpSharded(shard, log_n, moduli, n_q, n_p, dnum)
+    own = plan.own_limbs
+    own_q = [g for g in own if g < n_q]
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.int64)).cuda()
+    d_c = dev(c[own_q])
+    d_up = torch.zeros((dnum, len(own), N), dtype=torch.int64, device="cuda")
+    sp = lambda: torch.cuda.current_stream().cuda_stream
+    f = lambda: plan.run(d_c.data_ptr(), d_up.data_ptr(), stream=sp())
+    lib = pkg.lib()
+    l0 = lib.b200fhe_launch_count()
+    f()
+    torch.cuda.synchronize()
+    launches = int(lib.b200fhe_launch_count() - l0)
+    # parity gate: the unsharded key-switch ModUp on this rank's GPU (itself checked against the oracle in bench_sub.keyswitch_records / the tests)
+    ctx = pkg.Context(log_n, moduli, device=local)
+    ks = pkg.KeySwitch(ctx, n_q, n_p, dnum)
+    d_all, d_ref = dev(c), torch.zeros((dnum, total, N), dtype=torch.int64, device="cuda")
+    ks.modup(d_all.data_ptr(), d_ref.data_ptr(), stream=sp())
+    torch.cuda.synchronize()
+    ok = torch.tensor([1 if torch.equal(d_up, d_ref[:, own]) else 0], device="cuda")
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    parity = bool(int(ok.item()))
+    ks.close(); del d_all, d_ref, ctx
+    torch.cuda.empty_cache()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    step, graphed = f, False
+    if graph:
+        g = _graphed(torch, f)
+        if g is not None:
+            step, graphed = g, True
+    for _ in range(max(warmup, 3)):
+        step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    st = torch.cuda.current_stream()
+    e0.record(st)
+    for _ in range(steps):
+        step()
+    e1.record(st)
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    k_out = total - alpha
+    rec = {"workload": "C5: ModUp of one polynomial, N=2^%d, %d + %d limbs, dnum=%d, limb g on rank g %% %d, through b200fhe_modup_sharded (C ABI)"
+                       % (log_n, n_q, n_p, dnum, world),
+           "ms": ms, "value": 1e3 / ms, "unit": "polys/s", "n_gpus": world, "scaling": "strong", "cuda_graph": graphed,
+           "launches_per_call_per_rank": launches,
+           "collective": ("ncclAllGather of %d scaled limbs per digit (%d MiB), %d per call, on the plan's communication stream" % (alpha, alpha * N * 8 >> 20, dnum))
+                         if world > 1 else "none",
+           "work_per_call": {"limb_transforms": n_q + dnum * k_out, "bconv_mulmods": dnum * alpha * (1 + k_out) * N,
+                             "allgather_bytes": dnum * alpha * N * 8 if world > 1 else 0},
+           "parity_vs_unsharded": parity, "parity_scope": "every owned limb of every digit on every rank, bit-exact against b200fhe_keyswitch_modup"}
+    plan.close(); shard.close()
+    return rec

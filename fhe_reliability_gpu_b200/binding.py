@@ -62,6 +62,18 @@ SIGNATURES = {
     "b200fhe_keyswitch_apply": (i32, [vp, vp, vp, vp, vp, vp]),
     "b200fhe_keyswitch_apply_protected": (i32, [vp, vp, vp, vp, vp, vp, vp]),
     "b200fhe_keyswitch_set_inject": (i32, [vp, i32, vp, sz]),
+    "b200fhe_shard_unique_id": (i32, [C.POINTER(C.c_uint8)]),
+    "b200fhe_shard_init": (i32, [vp, i32, i32, C.POINTER(vp)]),
+    "b200fhe_shard_init_id": (i32, [C.POINTER(C.c_uint8), i32, i32, i32, C.POINTER(vp)]),
+    "b200fhe_shard_destroy": (i32, [vp]),
+    "b200fhe_shard_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "b200fhe_modup_sharded_layout": (i32, [i32, i32, i32, i32, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "b200fhe_modup_sharded_create": (i32, [vp, i32, U64P, i32, i32, i32, C.POINTER(vp)]),
+    "b200fhe_modup_sharded_destroy": (i32, [vp]),
+    "b200fhe_modup_sharded_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "b200fhe_modup_sharded": (i32, [vp, vp, vp, vp]),
+    "b200fhe_modup_sharded_scale": (i32, [vp, vp, vp, vp]),
+    "b200fhe_modup_sharded_raise": (i32, [vp, vp, C.POINTER(vp), vp, vp]),
     "b200fhe_ct_tensor": (i32, [vp, vp, vp, vp, sz, sz, vp]),
     "b200fhe_poly_add": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "b200fhe_poly_sub": (i32, [vp, vp, vp, sz, sz, sz, vp]),
@@ -460,3 +472,80 @@ def barrett_fold_host(q, a, b, fold, k=None, faults=(), propagate=0, device=0):
     check(lib().b200fhe_barrett_fold_host(q, _p(a), _p(b), _p(c), n_vec, vec_len, fold, k or 0, 1 if k else 0, propagate, arr, nf,
                                           _p(s1), _p(s2), v.ctypes.data_as(C.POINTER(C.c_uint32)), device))
     return c, s1, s2, (v if k else None)
+
+
+def modup_sharded_layout(n_q, n_p, dnum, world, rank):
+    """(own_limbs, source_order [dnum][alpha], counts [dnum][world]) of b200fhe_modup_sharded_layout (pure host)."""
+    alpha, total = n_q // dnum, n_q + n_p
+    nq, nt = i32(), i32()
+    own = (i32 * total)(); src = (i32 * (dnum * alpha))(); cnt = (i32 * (dnum * world))()
+    check(lib().b200fhe_modup_sharded_layout(n_q, n_p, dnum, world, rank, C.byref(nq), C.byref(nt), own, src, cnt))
+    return (list(own[:nt.value]), [list(src[d * alpha:(d + 1) * alpha]) for d in range(dnum)],
+            [list(cnt[d * world:(d + 1) * world]) for d in range(dnum)])
+
+
+class Shard:
+    """b200fhe_shard: this rank's place in the world (+ its NCCL communicator when world > 1).  `dist` = an initialised
+    torch.distributed (any backend) used only to hand rank 0's NCCL unique id to the other ranks."""
+
+    def __init__(self, rank=0, world=1, device=0, dist=None):
+        self.rank, self.world, self.device = rank, world, device
+        idb = (C.c_uint8 * 128)()
+        if world > 1 and dist is None:          # own transport: scale / raise halves only (b200fhe_shard_init with a NULL communicator)
+            import torch
+            torch.cuda.set_device(device)
+            h = vp()
+            check(lib().b200fhe_shard_init(None, rank, world, C.byref(h)))
+            self._h = h
+            return
+        if world > 1:
+            import torch
+            if rank == 0:
+                check(lib().b200fhe_shard_unique_id(idb))
+            t = torch.tensor(list(idb), dtype=torch.uint8)
+            if dist.get_backend() == "nccl":
+                t = t.cuda(device)
+            dist.broadcast(t, src=0)
+            idb = (C.c_uint8 * 128)(*[int(v) for v in t.cpu().tolist()])
+        h = vp()
+        check(lib().b200fhe_shard_init_id(idb, rank, world, device, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200fhe_shard_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+class ModUpSharded:
+    """b200fhe_modup_sharded plan of one rank."""
+
+    def __init__(self, shard, log_n, moduli, n_q, n_p, dnum):
+        self.shard, self.N, self.n_q, self.n_p, self.dnum = shard, 1 << log_n, n_q, n_p, dnum
+        arr = np.array([int(q) for q in moduli], dtype=np.uint64)
+        h = vp()
+        check(lib().b200fhe_modup_sharded_create(shard._h, log_n, _p(arr), n_q, n_p, dnum, C.byref(h)))
+        self._h = h
+        nq, nt = i32(), i32()
+        own = (i32 * (n_q + n_p))()
+        check(lib().b200fhe_modup_sharded_info(h, C.byref(nq), C.byref(nt), own))
+        self.n_own_q, self.n_own_total, self.own_limbs = nq.value, nt.value, list(own[:nt.value])
+
+    def run(self, d_c_own, d_up_own, stream=None):
+        check(lib().b200fhe_modup_sharded(self._h, d_c_own, d_up_own, stream))
+
+    def scale(self, d_c_own, d_y_own, stream=None):
+        check(lib().b200fhe_modup_sharded_scale(self._h, d_c_own, d_y_own, stream))
+
+    def raise_(self, d_c_own, y_full_ptrs, d_up_own, stream=None):
+        arr = (vp * len(y_full_ptrs))(*y_full_ptrs)
+        check(lib().b200fhe_modup_sharded_raise(self._h, d_c_own, arr, d_up_own, stream))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200fhe_modup_sharded_destroy(self._h)
+            self._h = None
+
+    __del__ = close

@@ -34,6 +34,12 @@ namespace b200 {
 
 struct FoldFault { u64 index; u64 payload; u32 product, kind; };
 
+struct FoldK { u32 k, c, M; };
+__host__ __device__ inline FoldK make_foldk(u32 k) {
+    u32 c = 2 * k;
+    while (2 * c <= 60) c *= 2;
+    return FoldK{k, c, (1u << k) + 1u};
+}
 struct FoldArgs {
     const u64 *a, *b;
     u64* c;
@@ -44,87 +50,136 @@ struct FoldArgs {
     const u32* fault_of;        // [n] 1 + index of the first fault on this element, 0 = none (NULL when no faults)
     u64 n, vec_len, groups_per_vec;
     u64 q, mu;
-    u32 K, fold, k, n_faults, propagate, checks;
+    u32 K, fold, n_faults, propagate;
+    FoldK F;
+    u32 rmu, rq;                // residues of the two constant operands
 };
 
-// residue of the 128-bit word (hi, lo) modulo M = 2^k + 1: alternating sum of its k-bit segments
-// (fold_mod_2k_plus_1_u64, outer_check.cpp:35-50, extended to two words).  ALU-pipe only.
-__device__ __forceinline__ u32 fold128(u64 lo, u64 hi, u32 k) {
-    const u32 M = (1u << k) + 1u;
-    const u64 mask = ((u64)1 << k) - 1;
-    long long acc = 0;
-    int sign = 1;
-    for (u32 pos = 0; pos < 128 && (lo | hi); pos += k) {
-        const u64 seg = lo & mask;
-        acc += sign > 0 ? (long long)seg : -(long long)seg;
-        sign = -sign;
-        lo = (lo >> k) | (hi << (64 - k));
-        hi >>= k;
-    }
-    long long r = acc % (long long)M;
-    if (r < 0) r += M;
+// residue of the 128-bit word (hi, lo) modulo M = 2^k + 1 (fold_mod_2k_plus_1_u64, outer_check.cpp:35-50, extended to two
+// words).  Shifts, masks and adds only (ALU pipe), no loop over the 128 / k segments: 2^(2k) = 1 (mod M), so first add up
+// the word's chunks of c = 2k 2^j bits (32 <= c <= 60, at most four of them), halve the chunk width down to 2k bits, and
+// finish with the one alternating step low k bits - high k bits.
+__device__ __forceinline__ u32 fold128(u64 lo, u64 hi, const FoldK& F) {
+    const u32 c = F.c;
+    const u64 mc = ((u64)1 << c) - 1;
+    u64 s = (lo & mc) + (((lo >> c) | (hi << (64 - c))) & mc) + ((hi >> (2 * c - 64)) & mc);
+    if (3 * c < 128) s += hi >> (3 * c - 64);
+    for (u32 w = c >> 1; w >= 2 * F.k; w >>= 1) s = (s & (((u64)1 << w) - 1)) + (s >> w);
+    const u32 w2 = 2 * F.k;
+    const u64 m2 = ((u64)1 << w2) - 1;
+    s = (s & m2) + (s >> w2);                      // the halvings leave at most a few carries above 2k bits
+    s = (s & m2) + (s >> w2);
+    int r = (int)(s & ((1u << F.k) - 1)) - (int)(s >> F.k);
+    if (r < 0) r += (int)F.M;
     return (u32)r;
 }
-__device__ __forceinline__ u32 mulres(u32 x, u32 y, u32 k) {          // x y mod 2^k + 1 for residues x, y <= 2^k, k <= 31
-    const u64 p = (u64)x * y;                                       // the check's own small multiply
-    return fold128(p, 0, k);
+__device__ __forceinline__ u32 mulres(u32 x, u32 y, const FoldK& F) {   // x y mod 2^k + 1 for residues x, y <= 2^k
+    return fold128((u64)x * y, 0, F);                                 // the check's own small multiply: 32 x 32 -> 64
 }
 
-template <bool CHECKS>
+// ALIGNED: fold is a power of two <= 256 dividing vec_len, so a group never straddles a CTA of 256 threads: its
+// signature / residue sums are reduced in the warp (and across warps through shared memory) and written with plain
+// stores -- no atomics, no clearing pass, the inter comparison done in place.  Otherwise: atomics + k_fold_finish.
+template <bool CHECKS, bool ALIGNED>
 __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
     const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = i < A.n;
     const u64 maskK = A.K >= 64 ? ~0ull : (((u64)1 << A.K) - 1);
-    u64 sig1 = 0, sig2 = 0, cval = 0;
+    const FoldK F = A.F;
+    u64 sig1 = 0, sig2 = 0;
     u32 bad = 0, pred = 0, obs = 0;
     if (live) {
         const u64 t = A.a[i] * A.b[i];                              // barrett_final.cpp:239: u64 ti = a * b
         u64 m1lo = t * A.mu, m1hi = __umul64hi(t, A.mu);            // mul1 = ti * mu (:127)
-        u64 c1lo = m1lo, c1hi = m1hi;                               // what the checks see
-        u32 fi = A.fault_of ? A.fault_of[i] : 0;
-        // faults on mul1
+        u64 c1lo = m1lo;                                            // what the checks see
+        const u64 c1hi = m1hi;
+        const u32 fi = A.fault_of ? A.fault_of[i] : 0;
         for (u32 f = fi; f && f <= A.n_faults && A.faults[f - 1].index == i; f++) {
-            const FoldFault F = A.faults[f - 1];
-            if (F.product != 1) continue;
-            c1lo = F.kind == 1 ? c1lo ^ (F.payload & maskK) : ((c1lo & ~maskK) | (F.payload & maskK));
+            const FoldFault X = A.faults[f - 1];
+            if (X.product != 1) continue;
+            c1lo = X.kind == 1 ? c1lo ^ (X.payload & maskK) : ((c1lo & ~maskK) | (X.payload & maskK));
         }
-        if (A.propagate) { m1lo = c1lo; m1hi = c1hi; }
+        if (A.propagate) m1lo = c1lo;
         const u32 sh = 2 * A.K;                                     // si = mul1 >> 2K (:131), 2K <= 120
         const u64 s = sh >= 64 ? (m1hi >> (sh - 64)) : ((m1lo >> sh) | (m1hi << (64 - sh)));
-        const u64 shi = sh >= 64 ? 0 : (m1hi >> sh);                // si fits one word whenever t < 2^64 and mu < 2^(K+1)
+        const u64 shi = sh >= 64 ? 0 : (m1hi >> sh);
         u64 m2lo = s * A.q, m2hi = __umul64hi(s, A.q) + shi * A.q;  // mul2 = si * q (:134)
-        u64 c2lo = m2lo, c2hi = m2hi;
+        u64 c2lo = m2lo;
+        const u64 c2hi = m2hi;
         for (u32 f = fi; f && f <= A.n_faults && A.faults[f - 1].index == i; f++) {
-            const FoldFault F = A.faults[f - 1];
-            if (F.product != 2) continue;
-            c2lo = F.kind == 1 ? c2lo ^ (F.payload & maskK) : ((c2lo & ~maskK) | (F.payload & maskK));
+            const FoldFault X = A.faults[f - 1];
+            if (X.product != 2) continue;
+            c2lo = X.kind == 1 ? c2lo ^ (X.payload & maskK) : ((c2lo & ~maskK) | (X.payload & maskK));
         }
-        if (A.propagate) { m2lo = c2lo; m2hi = c2hi; }
+        if (A.propagate) m2lo = c2lo;
         u64 ci = t - m2lo;                                          // (:138-139)
         const u64 cpre = ci;
         if (ci >= A.q) ci -= A.q;
-        cval = ci;
         A.c[i] = ci;
         sig1 = (c1lo & maskK) ^ (c2lo & maskK);                     // "instra" (:251-253)
         sig2 = ci & maskK;                                          // "sum"    (:254-257)
         if (CHECKS) {
-            const u32 k = A.k;
-            const u32 M = (1u << k) + 1u;
-            const u32 rt = fold128(t, 0, k), rmu = fold128(A.mu, 0, k), rq = fold128(A.q, 0, k);
-            const u32 r1 = fold128(c1lo, c1hi, k), r2 = fold128(c2lo, c2hi, k);
-            const u32 p1 = mulres(rt, rmu, k);
-            const u32 p2 = mulres(fold128(s, shi, k), rq, k);
+            const u32 M = F.M;
+            const u32 rt = fold128(t, 0, F);
+            const u32 r1 = fold128(c1lo, c1hi, F), r2 = fold128(c2lo, c2hi, F);
+            const u32 p1 = mulres(rt, A.rmu, F);
+            const u32 p2 = mulres(fold128(s, shi, F), A.rq, F);
             if (r1 != p1 || r2 != p2) bad |= 1;
             // subtraction: t == mul2 + c' as integers when mul2 <= t (always, fault-free)
-            const u32 rc = fold128(cpre, 0, k);
-            u32 rs = fold128(m2lo, 0, k) + rc;
+            u32 rs = fold128(m2lo, 0, F) + fold128(cpre, 0, F);
             if (rs >= M) rs -= M;
             if (m2hi == 0 && m2lo <= t && rs != rt) bad |= 4;
             pred = p1 + p2; if (pred >= M) pred -= M;
             obs = r1 + r2; if (obs >= M) obs -= M;
         }
     }
-    // group accumulation.  Whole warp inside one group: warp-reduce, one atomic per warp; otherwise per element.
+    if (ALIGNED) {
+        // n is a multiple of fold and fold divides 256: every group is complete and lives in this CTA
+        const u32 fold = A.fold, lane = threadIdx.x & 31;
+        u32 s1l = (u32)sig1, s1h = (u32)(sig1 >> 32), s2l = (u32)sig2, s2h = (u32)(sig2 >> 32);
+        const u32 span = fold < 32 ? fold : 32;
+        for (u32 o = span >> 1; o; o >>= 1) {
+            s1l ^= __shfl_xor_sync(0xffffffffu, s1l, o); s1h ^= __shfl_xor_sync(0xffffffffu, s1h, o);
+            s2l ^= __shfl_xor_sync(0xffffffffu, s2l, o); s2h ^= __shfl_xor_sync(0xffffffffu, s2h, o);
+            if (CHECKS) {
+                bad |= __shfl_xor_sync(0xffffffffu, bad, o);
+                pred += __shfl_xor_sync(0xffffffffu, pred, o);       // < 32 M < 2^32
+                obs += __shfl_xor_sync(0xffffffffu, obs, o);
+            }
+        }
+        if (fold <= 32) {
+            if (live && (lane & (fold - 1)) == 0) {
+                const u64 g = i / fold;
+                A.sig_intra[g] = ((u64)s1h << 32) | s1l;
+                A.sig_sum[g] = ((u64)s2h << 32) | s2l;
+                if (CHECKS) A.verdict[g] = bad | (pred % F.M != obs % F.M ? 2u : 0u);
+            }
+        } else {
+            __shared__ u32 sm[8][7];
+            const u32 warp = threadIdx.x >> 5;
+            if (lane == 0) {
+                sm[warp][0] = s1l; sm[warp][1] = s1h; sm[warp][2] = s2l; sm[warp][3] = s2h;
+                sm[warp][4] = bad; sm[warp][5] = pred % F.M; sm[warp][6] = obs % F.M;
+            }
+            __syncthreads();
+            const u32 wpg = fold >> 5, ngrp = 256 / fold;            // warps per group, groups per CTA
+            if (threadIdx.x < ngrp) {
+                const u64 g = ((u64)blockIdx.x * 256) / fold + threadIdx.x;
+                if (g * fold < A.n) {
+                    u32 v[7] = {0, 0, 0, 0, 0, 0, 0};
+                    for (u32 w = threadIdx.x * wpg; w < (threadIdx.x + 1) * wpg; w++) {
+                        v[0] ^= sm[w][0]; v[1] ^= sm[w][1]; v[2] ^= sm[w][2]; v[3] ^= sm[w][3];
+                        v[4] |= sm[w][4]; v[5] += sm[w][5]; v[6] += sm[w][6];
+                    }
+                    A.sig_intra[g] = ((u64)v[1] << 32) | v[0];
+                    A.sig_sum[g] = ((u64)v[3] << 32) | v[2];
+                    if (CHECKS) A.verdict[g] = v[4] | (v[5] % F.M != v[6] % F.M ? 2u : 0u);
+                }
+            }
+        }
+        return;
+    }
+    // general shapes: a warp that lies inside one group reduces first, one atomic per warp; otherwise per element
     const u64 vec = live ? i / A.vec_len : 0, within = live ? i % A.vec_len : 0;
     const u64 g = vec * A.groups_per_vec + within / A.fold;
     const u64 g0 = __shfl_sync(0xffffffffu, g, 0);
@@ -135,7 +190,7 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
         u32 anybad = 0, ps = 0, os = 0;
         if (CHECKS) {
             anybad = __reduce_or_sync(0xffffffffu, bad);
-            ps = __reduce_add_sync(0xffffffffu, pred);              // 32 residues < 2^32 / 32 each: k <= 26 fits; reduced below
+            ps = __reduce_add_sync(0xffffffffu, pred);
             os = __reduce_add_sync(0xffffffffu, obs);
         }
         if ((threadIdx.x & 31) == 0) {
@@ -143,9 +198,8 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
             atomicXor((unsigned long long*)&A.sig_sum[g], ((u64)hi2 << 32) | lo2);
             if (CHECKS) {
                 if (anybad) atomicOr(&A.verdict[g], anybad);
-                const u32 M = (1u << A.k) + 1u;
-                atomicAdd(&A.inter[2 * g], (unsigned long long)(ps % M));
-                atomicAdd(&A.inter[2 * g + 1], (unsigned long long)(os % M));
+                atomicAdd(&A.inter[2 * g], (unsigned long long)(ps % F.M));
+                atomicAdd(&A.inter[2 * g + 1], (unsigned long long)(os % F.M));
             }
         }
     } else if (live) {
@@ -157,10 +211,9 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
             atomicAdd(&A.inter[2 * g + 1], (unsigned long long)obs);
         }
     }
-    (void)cval;
 }
 
-// inter check: predicted vs observed residue sums of each group, compared once (outer_check.cpp:236-247)
+// inter check of the general path: predicted vs observed residue sums of each group, compared once (outer_check.cpp:236-247)
 __global__ void k_fold_finish(u32* verdict, const unsigned long long* inter, u64 groups, u32 k) {
     const u64 g = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= groups) return;
@@ -218,18 +271,26 @@ extern "C" int b200fhe_barrett_fold(uint64_t q, const uint64_t* d_a, const uint6
     if (checks && (k < 2 || k > 26)) return b200_set_err(B200FHE_EINVAL, "barrett_fold: residue width k must be in [2, 26]");
     if (!d_sig_intra || !d_sig_sum || (checks && !d_verdict)) return b200_set_err(B200FHE_EINVAL, "barrett_fold: null outputs");
     const size_t gpv = (vec_len + fold - 1) / fold, groups = gpv * n_vec;
+    const bool aligned = fold <= 256 && (fold & (fold - 1)) == 0 && vec_len % fold == 0;
     FoldArgs A{};
     A.a = (const u64*)d_a; A.b = (const u64*)d_b; A.c = (u64*)d_c; A.sig_intra = (u64*)d_sig_intra; A.sig_sum = (u64*)d_sig_sum; A.verdict = d_verdict;
-    A.n = n; A.vec_len = vec_len; A.groups_per_vec = gpv; A.q = q; A.mu = mu; A.K = (u32)K; A.fold = (u32)fold; A.k = (u32)k;
+    A.n = n; A.vec_len = vec_len; A.groups_per_vec = gpv; A.q = q; A.mu = mu; A.K = (u32)K; A.fold = (u32)fold;
     A.n_faults = (u32)n_faults; A.propagate = propagate ? 1 : 0;
-    cudaError_t e = cudaMemsetAsync(d_sig_intra, 0, groups * 8, s);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d_sig_sum, 0, groups * 8, s);
+    if (checks) {
+        A.F = make_foldk((u32)k);
+        A.rmu = (u32)(mu % A.F.M); A.rq = (u32)(q % A.F.M);
+    }
+    cudaError_t e = cudaSuccess;
     unsigned long long* d_inter = nullptr; FoldFault* d_f = nullptr; u32* d_of = nullptr;
-    if (e == cudaSuccess && checks) {
-        e = cudaMemsetAsync(d_verdict, 0, groups * 4, s);
-        if (e == cudaSuccess) e = cudaMallocAsync(&d_inter, groups * 16, s);
-        if (e == cudaSuccess) e = cudaMemsetAsync(d_inter, 0, groups * 16, s);
-        A.inter = d_inter;
+    if (!aligned) {
+        e = cudaMemsetAsync(d_sig_intra, 0, groups * 8, s);
+        if (e == cudaSuccess) e = cudaMemsetAsync(d_sig_sum, 0, groups * 8, s);
+        if (e == cudaSuccess && checks) {
+            e = cudaMemsetAsync(d_verdict, 0, groups * 4, s);
+            if (e == cudaSuccess) e = cudaMallocAsync(&d_inter, groups * 16, s);
+            if (e == cudaSuccess) e = cudaMemsetAsync(d_inter, 0, groups * 16, s);
+            A.inter = d_inter;
+        }
     }
     std::vector<FoldFault> fl;
     std::vector<u32> of;
@@ -252,11 +313,13 @@ extern "C" int b200fhe_barrett_fold(uint64_t q, const uint64_t* d_a, const uint6
         A.faults = d_f; A.fault_of = d_of;
     }
     if (e == cudaSuccess) {
-        if (checks) k_barrett_fold<true><<<blocks, 256, 0, s>>>(A);
-        else k_barrett_fold<false><<<blocks, 256, 0, s>>>(A);
+        if (checks && aligned) k_barrett_fold<true, true><<<blocks, 256, 0, s>>>(A);
+        else if (checks) k_barrett_fold<true, false><<<blocks, 256, 0, s>>>(A);
+        else if (aligned) k_barrett_fold<false, true><<<blocks, 256, 0, s>>>(A);
+        else k_barrett_fold<false, false><<<blocks, 256, 0, s>>>(A);
         b200_count_launches(1);
         e = cudaGetLastError();
-        if (e == cudaSuccess && checks) {
+        if (e == cudaSuccess && checks && !aligned) {
             k_fold_finish<<<(unsigned)((groups + 255) / 256), 256, 0, s>>>(d_verdict, d_inter, groups, (u32)k);
             b200_count_launches(1);
             e = cudaGetLastError();

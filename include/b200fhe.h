@@ -323,6 +323,50 @@ int b200fhe_keyswitch_apply_protected(b200fhe_keyswitch* plan, const uint64_t* d
  * ModUp conversion, dnum / dnum + 1 = the ModDown conversion of out[0] / out[1]; entries as in b200fhe_bconv_modup_protected. */
 int b200fhe_keyswitch_set_inject(b200fhe_keyswitch* plan, int conversion, const b200fhe_bconv_inject* inject, size_t n_inject);
 
+/* ---- limb-sharded ModUp over NCCL (config C5) -----------
+ * One process per GPU.  Limb g of Q u P (global order q_0..q_{n_q-1}, p_0..p_{n_p-1}) lives on rank g % world; a rank holds
+ * its limbs in ascending order.  The step replaced is the ModUp inside Phantom's relinearize_inplace / rotate_inplace
+ * (reliability_test/dotprod_test.cu:114,146), which the reference runs on one device. */
+typedef struct b200fhe_shard b200fhe_shard;
+typedef struct b200fhe_modup_plan b200fhe_modup_plan;
+
+/* ncclGetUniqueId on the calling rank; hand the 128 bytes to every rank (any transport) for b200fhe_shard_init_id. */
+int b200fhe_shard_unique_id(uint8_t id[128]);
+/* Adopt the caller's communicator: nccl_comm is an ncclComm_t whose rank / size are `rank` / `world`; the current CUDA
+ * device is the rank's GPU.  world = 1 takes NULL and never touches NCCL; NULL with world > 1 makes a shard for a caller
+ * with its own transport: plans on it support b200fhe_modup_sharded_scale / _raise only. */
+int b200fhe_shard_init(void* nccl_comm, int rank, int world, b200fhe_shard** out);
+/* Or let the library make it (ncclCommInitRank; collective over the world).  NCCL is resolved at run time
+ * (libnccl.so.2, override with B200FHE_NCCL_LIB); B200FHE_EUNSUPPORTED when it cannot be found. */
+int b200fhe_shard_init_id(const uint8_t id[128], int rank, int world, int device, b200fhe_shard** out);
+int b200fhe_shard_destroy(b200fhe_shard* shard);
+int b200fhe_shard_info(const b200fhe_shard* shard, int* rank, int* world, int* device, int* nccl_version);
+
+/* Ownership and gather layout, pure host arithmetic: own_limbs [n_own_total] = the rank's limbs ascending,
+ * source_order [dnum][alpha] = each digit's limbs in gather (rank-major) order, counts [dnum][world] = digit limbs per
+ * rank.  Any output may be NULL. */
+int b200fhe_modup_sharded_layout(int n_q, int n_p, int dnum, int world, int rank, int* n_own_q, int* n_own_total,
+                                 int* own_limbs, int* source_order, int* counts);
+
+/* Plan for one rank: `moduli` = the n_q + n_p moduli in GLOBAL order (the same array on every rank). */
+int b200fhe_modup_sharded_create(b200fhe_shard* shard, int log_n, const uint64_t* moduli, int n_q, int n_p, int dnum,
+                                 b200fhe_modup_plan** out);
+int b200fhe_modup_sharded_destroy(b200fhe_modup_plan* plan);
+int b200fhe_modup_sharded_info(const b200fhe_modup_plan* plan, int* n_own_q, int* n_own_total, int* own_limbs);
+
+/* ModUp of one polynomial: d_c_own [n_own_q][N] (NTT domain, the rank's limbs of Q) -> d_up_own [dnum][n_own_total][N]
+ * (NTT domain: digit d raised to the rank's limbs of Q u P; the digit's own limbs pass through).  Local inverse NTT with
+ * the conversion's scale step folded in, ONE all-gather per digit on the plan's communication stream (ncclAllGather, or a
+ * group of ncclBroadcast when the digit does not split evenly), contraction + forward NTT of digit d overlapping the
+ * gather of digit d + 1.  Only enqueues work (events order the two streams), so it can be captured in a CUDA graph.
+ * Collective: every rank calls it with the same plan parameters.  Bit-identical to b200fhe_keyswitch_modup. */
+int b200fhe_modup_sharded(b200fhe_modup_plan* plan, const uint64_t* d_c_own, uint64_t* d_up_own, void* stream);
+/* The two local halves, for a caller with its own transport: scale = step 1 (d_y_own [n_own_q][N], may alias d_c_own);
+ * raise = contraction + NTT given the gathered digits d_y_full[d] -> [alpha][N] in source_order. */
+int b200fhe_modup_sharded_scale(b200fhe_modup_plan* plan, const uint64_t* d_c_own, uint64_t* d_y_own, void* stream);
+int b200fhe_modup_sharded_raise(b200fhe_modup_plan* plan, const uint64_t* d_c_own, const uint64_t* const* d_y_full,
+                                uint64_t* d_up_own, void* stream);
+
 /* ---- evaluator steps around the key-switch (NTT-form polynomials [n_poly][L][N]) --------------------
  * The element-wise / permutation kernels phantom::multiply, add_inplace and rotate_inplace run around the
  * key-switch in reliability_test/dotprod_test.cu:113-152. */

@@ -119,20 +119,3 @@ def test_bconv_rejects_bad_arguments(pkg):
     with pytest.raises(pkg.B200FHEError):
         pkg.BaseConv(ctx, [], [1])
 
-
-def test_sharded_modup_over_nccl_matches_unsharded():
-    """Config C5 on 2 GPUs: bench_modup.py asserts, on every rank, that the limb-sharded pipeline
-    (one NCCL all-gather per digit) is bit-identical to the unsharded one.  Needs >= 2 devices."""
-    import os
-    import subprocess
-    import sys
-    import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (single-GPU boxes cover the same host logic through the gloo tests)")
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                        "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(root, "bench_modup.py"),
-                        "--log-n", "14", "--limbs", "12", "--special", "4", "--steps", "2"],
-                       capture_output=True, text=True, timeout=600)
-    assert p.returncode == 0, p.stderr[-2000:]
-    assert "bit-exact" in p.stdout

@@ -133,3 +133,19 @@ def test_shard_plan_layout():
     assert q.gather_counts(0) == ([1, 1, 0, 0], 1) and q.gathered_rows(0) == [0, 1]
     with pytest.raises(ValueError):
         ShardPlan(7, 2, 3, 2, 0)
+
+
+def test_c_abi_layout_matches_shard_plan():
+    """b200fhe_modup_sharded_layout (the C++ plan's ownership / gather order, pure host) == modup.ShardPlan."""
+    import fhe_reliability_gpu_b200 as pkg
+    from fhe_reliability_gpu_b200 import modup
+    for n_q, n_p, dnum in [(48, 16, 3), (12, 4, 3), (6, 2, 2), (4, 2, 2), (9, 3, 3), (8, 1, 1)]:
+        for world in (1, 2, 3, 4, 8):
+            for rank in range(world):
+                own, src, cnt = pkg.binding.modup_sharded_layout(n_q, n_p, dnum, world, rank)
+                plan = modup.ShardPlan(n_q, n_p, dnum, world, rank)
+                assert own == modup.owned(range(n_q + n_p), rank, world)
+                for d in range(dnum):
+                    assert src[d] == plan.source_order(d)
+                    assert cnt[d] == plan.gather_counts(d)[0]
+                    assert sorted(plan.my_digit_limbs(d) + plan.my_target_limbs(d)) == own
