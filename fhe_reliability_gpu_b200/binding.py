@@ -50,6 +50,7 @@ SIGNATURES = {
     "b200fhe_bconv_scale": (i32, [vp, vp, vp, sz, sz, vp]),
     "b200fhe_bconv_contract": (i32, [vp, vp, vp, sz, sz, vp]),
     "b200fhe_bconv_modup": (i32, [vp, vp, vp, vp]),
+    "b200fhe_bconv_modup_static": (i32, [vp, vp, vp, vp]),
     "b200fhe_bconv_modup_host": (i32, [vp, U64P, U64P]),
     "b200fhe_bconv_modup_protected": (i32, [vp, vp, vp, vp, vp, vp, sz, vp]),
     "b200fhe_bconv_modup_protected_host": (i32, [vp, U64P, U64P, C.POINTER(C.c_uint32), U64P, vp, sz]),
@@ -294,6 +295,10 @@ class BaseConv:
 
     def modup(self, in_ptr, out_ptr, stream=0):
         check(lib().b200fhe_bconv_modup(self._h, in_ptr, out_ptr, stream))
+
+    def modup_static(self, in_ptr, out_ptr, stream=0):
+        """b200fhe_bconv_modup_static: same conversion, scratch in the library's static device array (no allocation)."""
+        check(lib().b200fhe_bconv_modup_static(self._h, in_ptr, out_ptr, stream))
 
     def modup_host(self, x):
         """x [m][N] uint64 residues mod the source moduli -> [K][N] residues mod the targets."""

@@ -256,6 +256,17 @@ int b200fhe_bconv_contract(b200fhe_bconv* plan, const uint64_t* d_y, uint64_t* d
 int b200fhe_bconv_modup(b200fhe_bconv* plan, const uint64_t* d_in, uint64_t* d_out, void* stream);
 int b200fhe_bconv_modup_host(b200fhe_bconv* plan, const uint64_t* h_in, uint64_t* h_out);
 
+/* Allocation-free variant of b200fhe_bconv_modup.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result, bit for bit, as b200fhe_bconv_modup on a fast (HPS) plan; the [m][N] scratch between the scale and the
+ * contraction kernels is a file-scope `static __device__` array of B200FHE_STATIC_SCRATCH_WORDS 64-bit words (4 MiB) that
+ * every GPU loading the library holds until exit, so the call performs no cudaMalloc / cudaFree / allocating routine.
+ * m * N above that limit (or an exact-CRT plan) fails with B200FHE_EUNSUPPORTED and a message naming the limit.  Every call
+ * on a device shares the one array (nothing in it needs clearing: the scale kernel overwrites what the contraction reads),
+ * so calls that overlap on the GPU race -- serialise them on one stream. */
+#define B200FHE_STATIC_SCRATCH_WORDS (1u << 19)
+int b200fhe_bconv_modup_static(b200fhe_bconv* plan, const uint64_t* d_in, uint64_t* d_out, void* stream);
+
 /* ---- checksum-carrying base conversion ------------------------
  * rfhe_framewk/src/baseConv.py:42-98 bConv_ecc carries e_j = sum_i x_j[i] mod p_j through the conversion and
  * raises on a mismatch.  The device form checks the same linearity per kernel, with the sums accumulated inside the
