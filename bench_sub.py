@@ -218,7 +218,9 @@ def modup_sharded_record(pkg, torch, dist, rank, world, local, peak, log_n=17, n
             dist.barrier()
         torch.cuda.synchronize()
     step, graphed = f, False
-    if graph:
+    # world > 1 stays eager: capturing the call with the NCCL all-gather inside never returned on this stack (torch 2.11 /
+    # NCCL 2.28.9, both ranks capturing the same sequence; killed by the 300 s timeout in run r2g), so it is not attempted
+    if graph and world == 1:
         g = _graphed(torch, f)
         if g is not None:
             step, graphed = g, True
