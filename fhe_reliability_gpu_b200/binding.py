@@ -37,6 +37,8 @@ SIGNATURES = {
     "b200fhe_nwt_backward_host": (i32, [vp, U64P, sz, sz, sz]),
     "b200fhe_nwt_forward_protected": (i32, [vp, vp, sz, sz, sz, vp, vp, vp, sz, vp]),
     "b200fhe_nwt_forward_protected_host": (i32, [vp, U64P, sz, sz, sz, C.POINTER(C.c_uint32), U64P, vp, sz]),
+    "b200fhe_nwt_backward_protected": (i32, [vp, vp, sz, sz, sz, vp, vp, vp]),
+    "b200fhe_nwt_backward_protected_host": (i32, [vp, U64P, sz, sz, sz, C.POINTER(C.c_uint32), U64P]),
     "b200fhe_abft_weights": (i32, [vp, i32, U64P, U64P]),
     "b200fhe_four_step_protected_host": (i32, [u64, u64, sz, U64P, U64P, sz, U64P, C.POINTER(C.c_uint32), vp, sz, i32]),
     "b200fhe_relia_op_ranges": (i32, [sz, U64P, U64P, U64P]),
@@ -75,6 +77,20 @@ SIGNATURES = {
     "b200fhe_modup_sharded": (i32, [vp, vp, vp, vp]),
     "b200fhe_modup_sharded_scale": (i32, [vp, vp, vp, vp]),
     "b200fhe_modup_sharded_raise": (i32, [vp, vp, C.POINTER(vp), vp, vp]),
+    "b200fhe_bgv_create": (i32, [i32, U64P, i32, i32, u64, u64, i32, C.POINTER(vp)]),
+    "b200fhe_bgv_destroy": (i32, [vp]),
+    "b200fhe_bgv_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), U64P, U64P]),
+    "b200fhe_bgv_gen_secretkey": (i32, [vp]),
+    "b200fhe_bgv_gen_publickey": (i32, [vp]),
+    "b200fhe_bgv_encode": (i32, [vp, U64P, sz, U64P]),
+    "b200fhe_bgv_decode": (i32, [vp, U64P, U64P]),
+    "b200fhe_bgv_encrypt": (i32, [vp, U64P, vp]),
+    "b200fhe_bgv_decrypt": (i32, [vp, vp, i32, i32, u64, U64P]),
+    "b200fhe_bgv_multiply": (i32, [vp, vp, vp, vp, i32]),
+    "b200fhe_bgv_relinearize": (i32, [vp, vp, i32]),
+    "b200fhe_bgv_mod_switch_to_next": (i32, [vp, vp, i32, i32, vp, U64P]),
+    "b200fhe_bgv_rotate": (i32, [vp, vp, i32, i32, i32]),
+    "b200fhe_bgv_add": (i32, [vp, vp, vp, i32, i32]),
     "b200fhe_ct_tensor": (i32, [vp, vp, vp, vp, sz, sz, vp]),
     "b200fhe_poly_add": (i32, [vp, vp, vp, sz, sz, sz, vp]),
     "b200fhe_poly_sub": (i32, [vp, vp, vp, sz, sz, sz, vp]),
@@ -232,6 +248,19 @@ def _nwt_forward_protected_host(self, a, L=None, start_mod=0, plan=()):
     return a, verdict, sums
 
 
+def _nwt_backward_protected_host(self, a, L=None, start_mod=0):
+    """In-place protected inverse NTT of a [n_poly][L][N]; returns (a, verdict[n_limbs], sums[n_limbs][2]) with
+    sums = (evaluation-side checksum of the inputs, coefficient-side checksum of the outputs)."""
+    L = self.L if L is None else L
+    assert a.dtype == np.uint64 and a.flags.c_contiguous and a.size % (L * self.N) == 0
+    n_poly = a.size // (L * self.N)
+    verdict = np.zeros(n_poly * L, dtype=np.uint32)
+    sums = np.zeros((n_poly * L, 2), dtype=np.uint64)
+    check(lib().b200fhe_nwt_backward_protected_host(self._h, _p(a), n_poly, L, start_mod,
+                                                    verdict.ctypes.data_as(C.POINTER(C.c_uint32)), _p(sums)))
+    return a, verdict, sums
+
+
 def _abft_weights(self, idx):
     w = np.zeros(self.N, dtype=np.uint64); wh = np.zeros(self.N, dtype=np.uint64)
     check(lib().b200fhe_abft_weights(self._h, idx, _p(w), _p(wh)))
@@ -258,6 +287,7 @@ def _pmult_accum(self, ct_ptrs, pt_ptrs, out_ptr, n_poly, L=None, start_mod=0, a
 
 
 Context.nwt_forward_protected_host = _nwt_forward_protected_host
+Context.nwt_backward_protected_host = _nwt_backward_protected_host
 Context.abft_weights = _abft_weights
 Context.pmult_accum_host = _pmult_accum_host
 Context.pmult_accum = _pmult_accum
@@ -554,3 +584,82 @@ class ModUpSharded:
             self._h = None
 
     __del__ = close
+
+
+class Bgv:
+    """b200fhe_bgv: the BGV host roles + evaluator composition of dotprod_test.cu (context, keys, encoder, encrypt / decrypt,
+    multiply, relinearize, mod_switch_to_next, rotate, add).  Ciphertexts are device pointers [size][n_limbs][N]."""
+
+    def __init__(self, log_n, coeff_moduli, special_size, plain_modulus, seed=1, device=0):
+        arr = np.array([int(q) for q in coeff_moduli], dtype=np.uint64)
+        h = vp()
+        check(lib().b200fhe_bgv_create(log_n, _p(arr), len(arr), special_size, plain_modulus, seed, device, C.byref(h)))
+        self._h, self.N, self.t = h, 1 << log_n, int(plain_modulus)
+        self.n_q, self.n_p = len(arr) - special_size, special_size
+        check(lib().b200fhe_bgv_gen_secretkey(h))
+        check(lib().b200fhe_bgv_gen_publickey(h))
+
+    def encode(self, values):
+        v = np.ascontiguousarray(values, dtype=np.uint64)
+        out = np.zeros(self.N, dtype=np.uint64)
+        check(lib().b200fhe_bgv_encode(self._h, _p(v), v.size, _p(out)))
+        return out
+
+    def decode(self, plain):
+        out = np.zeros(self.N, dtype=np.uint64)
+        check(lib().b200fhe_bgv_decode(self._h, _p(np.ascontiguousarray(plain, dtype=np.uint64)), _p(out)))
+        return out
+
+    def encrypt(self, plain, d_ct):
+        check(lib().b200fhe_bgv_encrypt(self._h, _p(np.ascontiguousarray(plain, dtype=np.uint64)), d_ct))
+
+    def decrypt(self, d_ct, size, n_limbs, correction=1):
+        out = np.zeros(self.N, dtype=np.uint64)
+        check(lib().b200fhe_bgv_decrypt(self._h, d_ct, size, n_limbs, correction, _p(out)))
+        return out
+
+    def multiply(self, d_a, d_b, d_out, n_limbs):
+        check(lib().b200fhe_bgv_multiply(self._h, d_a, d_b, d_out, n_limbs))
+
+    def relinearize(self, d_ct, n_limbs):
+        check(lib().b200fhe_bgv_relinearize(self._h, d_ct, n_limbs))
+
+    def mod_switch_to_next(self, d_ct, size, n_limbs, d_out, correction=1):
+        cf = u64(correction)
+        check(lib().b200fhe_bgv_mod_switch_to_next(self._h, d_ct, size, n_limbs, d_out, C.byref(cf)))
+        return int(cf.value)
+
+    def rotate(self, d_ct, n_limbs, step, columns=False):
+        check(lib().b200fhe_bgv_rotate(self._h, d_ct, n_limbs, step, 1 if columns else 0))
+
+    def add(self, d_a, d_b, size, n_limbs):
+        check(lib().b200fhe_bgv_add(self._h, d_a, d_b, size, n_limbs))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().b200fhe_bgv_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
+def fault_payload(subtype, bitwidth, rng):
+    """XOR mask of one fault of the reference's taxonomy (rfhe_framewk/src/four_step_ntt_protected.cpp:163-245), for
+    b200fhe_inject kind 1 (computation fault on a butterfly product) or kind 3 (storage fault between the passes):
+      SCF-BF   one random bit below `bitwidth`                                   (:170-172, :186-188)
+      SCF-MBU  a burst of K adjacent bits, K in {2, 3, 4} (vectors: {2, 3})      (:173-178, :189-194)
+      MCF-PPE  one random bit (partial-product error)                            (:203-206, :233-235)
+      MCF-CTE  one bit of the upper half (carry-tree error)                      (:207-211)
+    MCF-CLE (a whole output line shifted by a multiple of one operand product, :212-222) belongs to the matrix-multiply
+    form of the prototype's stages and has no butterfly counterpart; it is not generated here.
+    rng: numpy Generator."""
+    if subtype in ("SCF-BF", "MCF-PPE"):
+        return 1 << int(rng.integers(0, bitwidth))
+    if subtype == "SCF-MBU":
+        K = int(rng.choice([2, 3, 4])) if bitwidth >= 4 else 2
+        start = int(rng.integers(0, max(0, bitwidth - K) + 1))
+        return ((1 << K) - 1) << start
+    if subtype == "MCF-CTE":
+        lo = max(1, bitwidth // 2)
+        return 1 << int(rng.integers(lo, max(lo, bitwidth - 1) + 1))
+    raise ValueError("unknown fault subtype %r" % (subtype,))

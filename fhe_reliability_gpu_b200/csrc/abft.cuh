@@ -60,6 +60,56 @@ struct AbftOut {
     }
 };
 
+// ---- the same two accumulators on the FP64 pipe ----------------------------------------------------------------------
+// The integer-multiply pipe is the binding unit of the transform; the FP64 pipe (one DFMA per 2 cycles per
+// sub-partition, its own pipe) is idle.  Integer-valued doubles below 2^53 multiply and add exactly, so the weighted sums
+// can be carried there at ZERO multiplier-pipe cost: a 32-bit piece p becomes the double 2^52 + p by pairing it with the
+// high word 0x43300000 (no instruction), one DADD removes the 2^52, DFMA accumulates.
+//   input side : w (< 2^12) x the two 32-bit halves of the word: 44-bit products, up to 32 terms      (< 2^49)
+//   output side: omega's 30-bit halves x the three 20-bit pieces of the canonical output: 50-bit products, 8 terms per
+//                accumulator (two accumulator sets, even / odd outputs)                                (< 2^53)
+// The sums are converted back to integers once per thread; from there on the path is the integer one (same 128-bit value).
+__device__ __forceinline__ double abft_dbl(u32 piece) { return __hiloint2double(0x43300000, (int)piece) - 4503599627370496.0; }
+
+struct AbftInF {
+    double lo = 0.0, hi = 0.0;
+    __device__ __forceinline__ void add(double w, u64 x) {
+        u32 xl, xh;
+        unpack64(x, xl, xh);
+        lo = fma(w, abft_dbl(xl), lo);
+        hi = fma(w, abft_dbl(xh), hi);
+    }
+    __device__ __forceinline__ void value(u64& s0, u64& s1) const {
+        const u64 l = __double2ull_rn(lo), h = __double2ull_rn(hi);
+        s0 = l + (h << 32);
+        s1 = (h >> 32) + (s0 < l);
+    }
+};
+
+struct AbftOutF {
+    double p[2][6] = {};
+    // om = omega0 | omega1 << 32 (30-bit halves), x canonical (< 2^60); set = 0 / 1 alternates so each accumulator sees 8 terms
+    __device__ __forceinline__ void add(int set, u64 om, u64 x) {
+        u32 o0, o1;
+        unpack64(om, o0, o1);
+        const double a0 = abft_dbl(o0), a1 = abft_dbl(o1);
+        const double x0 = abft_dbl((u32)x & 0xfffffu), x1 = abft_dbl((u32)(x >> 20) & 0xfffffu), x2 = abft_dbl((u32)(x >> 40));
+        p[set][0] = fma(a0, x0, p[set][0]); p[set][1] = fma(a0, x1, p[set][1]); p[set][2] = fma(a0, x2, p[set][2]);
+        p[set][3] = fma(a1, x0, p[set][3]); p[set][4] = fma(a1, x1, p[set][4]); p[set][5] = fma(a1, x2, p[set][5]);
+    }
+    // sum_{i,j} P_ij 2^(30 i + 20 j)  < 2^125
+    __device__ __forceinline__ void value(u64& s0, u64& s1) const {
+        unsigned __int128 t = 0;
+#pragma unroll
+        for (int i = 0; i < 2; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++)
+                t += (unsigned __int128)(__double2ull_rn(p[0][3 * i + j]) + __double2ull_rn(p[1][3 * i + j])) << (30 * i + 20 * j);
+        s0 = (u64)t;
+        s1 = (u64)(t >> 64);
+    }
+};
+
 // counters: [limb][side][8] u64, side 0 = input sum, 1 = output sum.  The 128-bit per-thread sum
 // (s1:s0) is committed unreduced as NDIG 26-bit digits: one REDUX per digit per warp and one atomic per
 // digit per CTA (-DB200_ABFT_WARP_COMMIT: per warp, the r1c form; 17.9 % -> 16.6 % overhead at C2's shape);

@@ -467,10 +467,17 @@ extern "C" int b200fhe_abft_weights(b200fhe_ctx* c, int idx, uint64_t* w, uint64
     return 0;
 }
 
-extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, uint32_t* d_verdict,
-                                             uint64_t* d_sums, const b200fhe_inject* plan, size_t n_plan, void* stream) {
+__global__ void k_xor_word(u64* p, u64 mask) { *p ^= mask; }
+
+static int nwt_protected_impl(bool inverse, b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, uint32_t* d_verdict,
+                              uint64_t* d_sums, const b200fhe_inject* plan, size_t n_plan, void* stream) {
     int rc = check_limbs(c, L, start, "nwt_protected");
     if (rc) return rc;
+    if (inverse) {
+        if (n_plan) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt_backward_protected: fault injection is defined for the forward transform only");
+        for (size_t i = start; i < start + L; i++)
+            if (!c->has_inverse[i]) return b200_set_err(B200FHE_EINVAL, "nwt_backward_protected: no inverse tables for modulus %zu", i);
+    }
     if (n_poly == 0 || L == 0) return 0;
     if (!d || !d_verdict) return b200_set_err(B200FHE_EINVAL, "nwt_protected: null argument");
     if (n_plan > B200FHE_MAX_INJECT || (n_plan && !plan)) return b200_set_err(B200FHE_EINVAL, "nwt_protected: bad injection plan");
@@ -488,18 +495,25 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
         c->abft_dirty &= ~(1u << slot);
     }
     InjEntry h[B200FHE_MAX_INJECT];
+    std::vector<b200fhe_inject> storage;        // kind 3 entries
+    size_t n_bf = 0;                             // butterfly-product entries (kinds 1, 2)
     for (size_t i = 0; i < n_plan; i++) {
+        if (plan[i].kind == 3) {               // storage fault between the passes: not a butterfly, handled below
+            if (plan[i].limb >= n_limbs || plan[i].butterfly >= c->N || c->log_n < 12)
+                return b200_set_err(B200FHE_EINVAL, "nwt_protected: storage fault %zu out of range (needs N >= 2^12)", i);
+            storage.push_back(plan[i]);
+            continue;
+        }
         if (plan[i].limb >= n_limbs || plan[i].stage >= (uint32_t)c->log_n || plan[i].butterfly >= c->N / 2 || plan[i].kind < 1 || plan[i].kind > 2)
             return b200_set_err(B200FHE_EINVAL, "nwt_protected: injection %zu out of range", i);
         const uint64_t gap = c->N >> (plan[i].stage + 1);
-        h[i].limb = plan[i].limb;
-        h[i].stage = plan[i].stage;
-        h[i].xa = (u32)(2 * (plan[i].butterfly / gap) * gap + plan[i].butterfly % gap);
-        h[i].kind = plan[i].kind;
-        h[i].payload = plan[i].payload;
+        InjEntry* hp = h + n_bf++;
+        hp->limb = plan[i].limb; hp->stage = plan[i].stage;
+        hp->xa = (u32)(2 * (plan[i].butterfly / gap) * gap + plan[i].butterfly % gap);
+        hp->kind = plan[i].kind; hp->payload = plan[i].payload;
     }
-    if (n_plan) {
-        CK(cudaMemcpyAsync(d_inj, h, sizeof(InjEntry) * n_plan, cudaMemcpyHostToDevice, s));
+    if (n_bf) {
+        CK(cudaMemcpyAsync(d_inj, h, sizeof(InjEntry) * n_bf, cudaMemcpyHostToDevice, s));
         CK(cudaStreamSynchronize(s));           // h[] is a stack buffer
     }
     c->abft_dirty |= (1u << slot);              // cleared once finalize (which zeroes the counters) is enqueued
@@ -511,22 +525,32 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
     const int big = (all_near && !getenv("B200FHE_NO_NEAR")) ? 2 : all_big ? 1 : 0;
     PassArgs a;
     a.mods = c->d_mods;
-    a.tw = c->d_tw;
-    a.rtw = c->d_rtw;
+    a.tw = inverse ? c->d_itw : c->d_tw;
+    a.rtw = inverse ? c->d_irtw : c->d_rtw;
     a.N = (u32)c->N;
     a.L = (u32)L;
     a.start_mod = (u32)start;
     a.omega = (const u64*)c->d_omega;
     a.abft = d_cnt;
     a.inj = d_inj;
-    a.n_inj = (u32)n_plan;
+    a.n_inj = (u32)n_bf;
     size_t step = chunk_polys(c, L);
     if (step * L > 32768) step = 32768 / L ? 32768 / L : 1;
     for (size_t p0 = 0; p0 < n_poly; p0 += step) {
         const size_t np = n_poly - p0 < step ? n_poly - p0 : step;
         a.data = (u64*)d + p0 * L * c->N;
         a.limb0 = (u32)(p0 * L);
-        rc = launch_ntt_protected(big, a, c->log_n, (u32)(np * L), s);
+        if (!storage.empty()) {
+            // pass 1, the stored intermediate words XOR-ed in HBM (the 2D transform's round trip: the SCF site of a GPU), pass 2
+            rc = launch_ntt_protected(big, a, c->log_n, (u32)(np * L), s, 1);
+            for (const b200fhe_inject& f : storage)
+                if (!rc && f.limb >= p0 * L && f.limb < (p0 + np) * L) {
+                    k_xor_word<<<1, 1, 0, s>>>((u64*)d + (size_t)f.limb * c->N + f.butterfly, f.payload);
+                    g_launches += 1;
+                }
+            if (!rc) rc = launch_ntt_protected(big, a, c->log_n, (u32)(np * L), s, 2);
+        } else
+        rc = inverse ? launch_ntt_protected_inverse(big, a, c->log_n, (u32)(np * L), s) : launch_ntt_protected(big, a, c->log_n, (u32)(np * L), s);
         if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt_protected: log_n=%d unsupported (rc=%d)", c->log_n, rc);
         g_launches += c->log_n <= 11 ? 1 : 2;
     }
@@ -537,8 +561,17 @@ extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t
     return 0;
 }
 
-extern "C" int b200fhe_nwt_forward_protected_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start, uint32_t* h_verdict,
-                                                  uint64_t* h_sums, const b200fhe_inject* plan, size_t n_plan) {
+extern "C" int b200fhe_nwt_forward_protected(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, uint32_t* d_verdict,
+                                             uint64_t* d_sums, const b200fhe_inject* plan, size_t n_plan, void* stream) {
+    return nwt_protected_impl(false, c, d, n_poly, L, start, d_verdict, d_sums, plan, n_plan, stream);
+}
+extern "C" int b200fhe_nwt_backward_protected(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, uint32_t* d_verdict,
+                                              uint64_t* d_sums, void* stream) {
+    return nwt_protected_impl(true, c, d, n_poly, L, start, d_verdict, d_sums, nullptr, 0, stream);
+}
+
+static int nwt_protected_host_impl(bool inverse, b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start, uint32_t* h_verdict,
+                                   uint64_t* h_sums, const b200fhe_inject* plan, size_t n_plan) {
     int rc = check_limbs(c, L, start, "nwt_protected_host");
     if (rc) return rc;
     if (n_poly == 0 || L == 0) return 0;
@@ -553,13 +586,22 @@ extern "C" int b200fhe_nwt_forward_protected_host(b200fhe_ctx* c, uint64_t* h, s
     uint32_t* d_verdict = reinterpret_cast<uint32_t*>(d_sums + 2 * n_limbs);
     cudaStream_t s = c->own_stream;
     CK(cudaMemcpyAsync(c->d_stage, h, words * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
-    rc = b200fhe_nwt_forward_protected(c, c->d_stage, n_poly, L, start, d_verdict, d_sums, plan, n_plan, s);
+    rc = nwt_protected_impl(inverse, c, c->d_stage, n_poly, L, start, d_verdict, d_sums, plan, n_plan, s);
     if (rc) return rc;
     CK(cudaMemcpyAsync(h, c->d_stage, words * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(h_verdict, d_verdict, n_limbs * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     if (h_sums) CK(cudaMemcpyAsync(h_sums, d_sums, 2 * n_limbs * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     return 0;
+}
+
+extern "C" int b200fhe_nwt_forward_protected_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start, uint32_t* h_verdict,
+                                                  uint64_t* h_sums, const b200fhe_inject* plan, size_t n_plan) {
+    return nwt_protected_host_impl(false, c, h, n_poly, L, start, h_verdict, h_sums, plan, n_plan);
+}
+extern "C" int b200fhe_nwt_backward_protected_host(b200fhe_ctx* c, uint64_t* h, size_t n_poly, size_t L, size_t start, uint32_t* h_verdict,
+                                                   uint64_t* h_sums) {
+    return nwt_protected_host_impl(true, c, h, n_poly, L, start, h_verdict, h_sums, nullptr, 0);
 }
 
 // ---------------------------------------------------------------- pmult

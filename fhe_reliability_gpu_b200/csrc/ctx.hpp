@@ -43,7 +43,9 @@ struct PassArgs {
 // mode: 0 = any modulus, 1 = q >= 2^36 (BIG), 2 = q = 2^bits - delta (NEAR)
 int launch_ntt(bool inverse, int big, const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s);
 // protected forward transform (a.omega / a.abft set); counters must be zero on entry
-int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s);
+int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s, int mask = 3);
+// protected inverse transform: a.tw / a.rtw are the inverse tables; side 0 = evaluation-side sum, side 1 = coefficient-side sum
+int launch_ntt_protected_inverse(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s);
 // verdict[i] = (input checksum != output checksum); sums (optional) [n][2]; zeroes the counters
 void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s);
 

@@ -69,7 +69,7 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 // registers) spills and measured no faster; 512-row columns (LC = 9) fit 2
 __host__ __device__ constexpr int col_min_ctas(int LC, bool inverse) { return LC >= 9 ? 2 : 3; }
 template <int LC, int LA, int BIG, bool PROT, bool INJ>
-__global__ void __launch_bounds__(kTile * col_groups(LC, LA), (PROT || INJ) ? 1 : col_min_ctas(LC, false))
+__global__ void __launch_bounds__(kTile * col_groups(LC, LA), INJ ? 1 : col_min_ctas(LC, false))
 k_fwd_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
     static_assert(NG >= RB, "the first phase runs in one sweep");
@@ -95,13 +95,20 @@ k_fwd_col(PassArgs p) {
     __syncthreads();
     if (g < RB) {
         if constexpr (PROT) {
+            constexpr int pl = (LC + kRowLog + 1) / 2;
+            static_assert(pl <= LB + kRowLog, "the weights of a thread's elements are affine in e");
+#ifdef B200_ABFT_INT                 // the r1 form: weighted products on the integer-multiply pipe
             AbftIn acc;
-            const int pl = (LC + kRowLog + 1) / 2;
 #pragma unroll
-#ifdef B200_ABL_ABFT_NOIN            // timing ablation: no weighted products on the input side
-            for (int e = 0; e < RA; e++) acc.lo ^= v[e];
-#else
             for (int e = 0; e < RA; e++) acc.add(abft_w((u32)(e * RB + g) * kRowLen + col, pl), v[e]);
+#else
+            // element e sits at index i0 + e (RB 256), and 2^pl divides RB 256: w_e = w_0 + e D  (abft_w = i mod 2^pl + i div 2^pl + 2)
+            AbftInF acc;
+            const u32 i0 = (u32)g * kRowLen + col;
+            double wd = (double)abft_w(i0, pl);
+            const double dd = (double)((RB * kRowLen) >> pl);
+#pragma unroll
+            for (int e = 0; e < RA; e++) { acc.add(wd, v[e]); wd += dd; asm("" : "+d"(wd)); }   // keep the DADD chain (else 16 I2F.F64)
 #endif
             acc.value(ck0, ck1);
         }
@@ -252,6 +259,7 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_r
         // output side of the checksum, on the values just stored
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         const u32 a0 = cl * 128 + ((cl & 7) << 4);
+#ifdef B200_ABFT_INT
         AbftOut acc;
 #pragma unroll
         for (int c = 0; c < 8; c++) {
@@ -259,13 +267,25 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_r
             acc.add(o.x, v[2 * c]);
             acc.add(o.y, v[2 * c + 1]);
         }
+#else
+        AbftOutF acc;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const ulonglong2 o = *reinterpret_cast<const ulonglong2*>(xrow + (a0 ^ (c << 4)));
+            acc.add(0, o.x, v[2 * c]);
+            acc.add(1, o.y, v[2 * c + 1]);
+        }
+#endif
         u64 s0, s1;
         acc.value(s0, s1);
         abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1, pslot, NP);
     }
 }
 
-template <int BIG, int NP>
+// PROT: the protected inverse transform -- the identity of the forward one read backwards: the inputs here are the
+// evaluations (SEAL order), so this pass accumulates sum_k omega_k a^_k on the words it loads (dense weights: FP64 pipe),
+// and the column pass accumulates sum_i w_i a_i on the coefficients it stores.
+template <int BIG, int NP, bool PROT>
 __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
     RowSmem<NP>& s = *reinterpret_cast<RowSmem<NP>*>(smraw);
@@ -286,9 +306,26 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_r
     const ulonglong2* in = reinterpret_cast<const ulonglong2*>(rowp + cl * 16);
 #pragma unroll
     for (int e = 0; e < 8; e++) { ulonglong2 x = in[e]; v[2 * e] = x.x; v[2 * e + 1] = x.y; }
-    __syncthreads();
+    if constexpr (PROT) {
+        // every loaded word is taken mod q (the transform's contract), and it is that canonical value the checksum weighs
+        const ulonglong2* om = reinterpret_cast<const ulonglong2*>(p.omega + (size_t)mi * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen + cl * 16);
+        AbftOutF acc;
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const ulonglong2 o = __ldg(om + e);
+            v[2 * e] = BIG ? canon2(reduce_lazy<BIG>(v[2 * e], m), m.q) : canon3(reduce_lazy<BIG>(v[2 * e], m), m.q);
+            v[2 * e + 1] = BIG ? canon2(reduce_lazy<BIG>(v[2 * e + 1], m), m.q) : canon3(reduce_lazy<BIG>(v[2 * e + 1], m), m.q);
+            acc.add(0, o.x, v[2 * e]);
+            acc.add(1, o.y, v[2 * e + 1]);
+        }
+        u64 s0, s1;
+        acc.value(s0, s1);
+        abft_commit<5>(p.abft, p.limb0 + limb, 0, s0, s1, pslot, NP);      // contains the __syncthreads the barrier needs
+    } else {
+        __syncthreads();
+    }
     mbar_wait(&s.bar, 0);
-    gs_phase<4, BIG, false, 0, kGsT>(v, TwList<kRowSlice>{s.twB + tslice}, m);
+    gs_phase<4, BIG, false, PROT ? 1 : 0, kGsT>(v, TwList<kRowSlice>{s.twB + tslice}, m);
     unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + (pslot * kRowsPerCta + rl) * (kRowLen * 8);
     {
         const u32 a0 = cl * 128 + ((cl & 7) << 4);
@@ -302,13 +339,15 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_r
 #pragma unroll
         for (int e = 0; e < 16; e++) v[e] = *reinterpret_cast<const u64*>(xrow + e * 128 + (b0 ^ ((e & 7) << 4)));
     }
-    gs_phase<4, BIG, false, inv_row_b1<BIG>(), kGsT>(v, TwList<1>{s.twA + rl * 16}, m);
+    constexpr int b1 = PROT ? gs_out_bound<4, BIG, false, 1, kGsT>() : inv_row_b1<BIG>();
+    static_assert(gs_out_bound<4, BIG, false, b1, kGsT>() <= inv_row_b2<BIG>(), "the column pass assumes inv_row_b2");
+    gs_phase<4, BIG, false, b1, kGsT>(v, TwList<1>{s.twA + rl * 16}, m);
 #pragma unroll
     for (int e = 0; e < 16; e++) rowp[e * 16 + cl] = v[e];
 }
 
 // ---------------------------------------------------------------- inverse, columns
-template <int LC, int LA, int BIG>
+template <int LC, int LA, int BIG, bool PROT>
 __global__ void __launch_bounds__(kTile * col_groups(LC, LA), col_min_ctas(LC, true))
 k_inv_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
@@ -323,6 +362,7 @@ k_inv_col(PassArgs p) {
     u64* base = p.data + (size_t)limb * p.N + tile * kTile;
     const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
     ulonglong2* stw = reinterpret_cast<ulonglong2*>(sm + (LB > 0 ? (kTile << LC) : 0));
+    u64 ck0 = 0, ck1 = 0;
     for (int i = threadIdx.x; i < (1 << LC); i += blockDim.x) stw[i] = __ldg(itw + i);
     if constexpr (LB == 0) __syncthreads();
     if constexpr (LB > 0) {
@@ -364,7 +404,19 @@ k_inv_col(PassArgs p) {
         gs_phase<LA, BIG, true, (LB > 0 ? gs_out_bound<(LB > 0 ? LB : 1), BIG, false, inv_row_b2<BIG>(), kGsT>() : inv_row_b2<BIG>()), 0>(v, TwShared{stw, 1u}, m);
 #pragma unroll
         for (int e = 0; e < RA; e++) base[(size_t)(e * RB + g) * kRowLen + c] = v[e];
+        if constexpr (PROT) {
+            // coefficient side of the checksum on the canonical values just stored; weights affine in e as in k_fwd_col
+            constexpr int pl = (LC + kRowLog + 1) / 2;
+            static_assert(pl <= LB + kRowLog, "the weights of a thread's elements are affine in e");
+            AbftInF acc;
+            double wd = (double)abft_w((u32)g * kRowLen + tile * kTile + c, pl);
+            const double dd = (double)((RB * kRowLen) >> pl);
+#pragma unroll
+            for (int e = 0; e < RA; e++) { acc.add(wd, v[e]); wd += dd; asm("" : "+d"(wd)); }   // keep the DADD chain (else 16 I2F.F64)
+            acc.value(ck0, ck1);
+        }
     }
+    if constexpr (PROT) abft_commit<4>(p.abft, p.limb0 + limb, 1, ck0, ck1);
 }
 
 // ---------------------------------------------------------------- small N (2 <= N <= 2^11)
@@ -380,12 +432,15 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
     const u32 N = p.N;
     const u64 nq = 0 - m.q;
     AbftIn ain;
+    AbftOut aev;
     for (u32 i = threadIdx.x; i < N; i += blockDim.x) {
         const u64 x = base[i];
-        if (PROT) ain.add(abft_w(i, (logn + 1) / 2), x);
+        if (PROT && !INVERSE) ain.add(abft_w(i, (logn + 1) / 2), x);
         a[i] = canon3(reduce_lazy<false>(x, m), m.q);
+        if (PROT && INVERSE) aev.add(p.omega[(size_t)mi * N + i], a[i]);      // evaluation side: sum_k omega_k a^_k
     }
-    if (PROT) { u64 s0, s1; ain.value(s0, s1); abft_commit<4>(p.abft, p.limb0 + limb, 0, s0, s1); }
+    if (PROT && !INVERSE) { u64 s0, s1; ain.value(s0, s1); abft_commit<4>(p.abft, p.limb0 + limb, 0, s0, s1); }
+    if (PROT && INVERSE) { u64 s0, s1; aev.value(s0, s1); abft_commit<5>(p.abft, p.limb0 + limb, 0, s0, s1); }
     __syncthreads();
     if (!INVERSE) {
         for (int s = 0; s < logn; s++) {
@@ -419,11 +474,14 @@ __global__ void __launch_bounds__(256) k_small(PassArgs p, int logn) {
         __syncthreads();
     }
     AbftOut aout;
+    AbftIn acf;
     for (u32 i = threadIdx.x; i < N; i += blockDim.x) {
         base[i] = a[i];
-        if (PROT) aout.add(p.omega[(size_t)mi * N + i], a[i]);
+        if (PROT && !INVERSE) aout.add(p.omega[(size_t)mi * N + i], a[i]);
+        if (PROT && INVERSE) acf.add(abft_w(i, (logn + 1) / 2), a[i]);        // coefficient side: sum_i w_i a_i
     }
-    if (PROT) { u64 s0, s1; aout.value(s0, s1); abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1); }
+    if (PROT && !INVERSE) { u64 s0, s1; aout.value(s0, s1); abft_commit<5>(p.abft, p.limb0 + limb, 1, s0, s1); }
+    if (PROT && INVERSE) { u64 s0, s1; acf.value(s0, s1); abft_commit<4>(p.abft, p.limb0 + limb, 1, s0, s1); }
 }
 
 // one thread per (limb, side): recombine the digit sums (Horner, Barrett per step) and clear the counters;
@@ -485,18 +543,18 @@ static int launch_fwd_row(PassArgs a, u32 np, cudaStream_t s) {
     }
     return 0;
 }
-template <int BIG>
+template <int BIG, bool PROT = false>
 static int launch_inv_row(PassArgs a, u32 np, cudaStream_t s) {
     const u32 tiles = (a.N >> kRowLog) / kRowsPerCta, pairs = g_row_pairs ? np / 2 : 0;
     if (pairs) {
-        if (set_smem_once<k_inv_row<BIG, 2>>(sizeof(RowSmem<2>)) != cudaSuccess) return -4;
+        if (set_smem_once<k_inv_row<BIG, 2, PROT>>(sizeof(RowSmem<2>)) != cudaSuccess) return -4;
         a.n_poly = pairs * 2; a.poly0 = 0;
-        k_inv_row<BIG, 2><<<dim3(tiles * pairs, a.L), kRowSlice * 2, sizeof(RowSmem<2>), s>>>(a);
+        k_inv_row<BIG, 2, PROT><<<dim3(tiles * pairs, a.L), kRowSlice * 2, sizeof(RowSmem<2>), s>>>(a);
     }
     if (np - 2 * pairs) {
-        if (set_smem_once<k_inv_row<BIG, 1>>(sizeof(RowSmem<1>)) != cudaSuccess) return -4;
+        if (set_smem_once<k_inv_row<BIG, 1, PROT>>(sizeof(RowSmem<1>)) != cudaSuccess) return -4;
         a.n_poly = np - 2 * pairs; a.poly0 = 2 * pairs;
-        k_inv_row<BIG, 1><<<dim3(tiles * a.n_poly, a.L), kRowSlice, sizeof(RowSmem<1>), s>>>(a);
+        k_inv_row<BIG, 1, PROT><<<dim3(tiles * a.n_poly, a.L), kRowSlice, sizeof(RowSmem<1>), s>>>(a);
     }
     return 0;
 }
@@ -515,7 +573,7 @@ static int launch_fwd2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t
     if (mask & 2) return launch_fwd_row<BIG, PROT, INJ>(a, np, s);
     return 0;
 }
-template <int LC, int LA, int BIG>
+template <int LC, int LA, int BIG, bool PROT = false>
 static int launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
     const u32 np = n_limbs / a_in.L;
@@ -523,13 +581,13 @@ static int launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t
     a.n_poly = np;
     dim3 gc((kRowLen / kTile) * np, a.L);
     if (mask & 1) {
-        int rc = launch_inv_row<BIG>(a, np, s);
+        int rc = launch_inv_row<BIG, PROT>(a, np, s);
         if (rc) return rc;
     }
     constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
     if (mask & 2) {
-        if (set_smem_once<k_inv_col<LC, LA, BIG>>(smem) != cudaSuccess) return -4;
-        k_inv_col<LC, LA, BIG><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
+        if (set_smem_once<k_inv_col<LC, LA, BIG, PROT>>(smem) != cudaSuccess) return -4;
+        k_inv_col<LC, LA, BIG, PROT><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
     }
     return 0;
 }
@@ -584,35 +642,69 @@ int launch_ntt(bool inverse, int big, const PassArgs& a, int logn, u32 n_limbs, 
 }
 
 template <int BIG, bool INJ>
-static int launch_prot_t(const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+static int launch_prot_t(const PassArgs& a, int logn, u32 n_limbs, int mask, cudaStream_t s) {
     switch (logn) {
 #ifndef B200_FAST_BUILD
-        case 12: return launch_fwd2<4, 4, BIG, true, INJ>(a, n_limbs, 3, s);
-        case 13: return launch_fwd2<5, 3, BIG, true, INJ>(a, n_limbs, 3, s);
-        case 14: return launch_fwd2<6, 3, BIG, true, INJ>(a, n_limbs, 3, s);
-        case 15: return launch_fwd2<7, 4, BIG, true, INJ>(a, n_limbs, 3, s);
-        case 17: return launch_fwd2<9, 5, BIG, true, INJ>(a, n_limbs, 3, s);
+        case 12: return launch_fwd2<4, 4, BIG, true, INJ>(a, n_limbs, mask, s);
+        case 13: return launch_fwd2<5, 3, BIG, true, INJ>(a, n_limbs, mask, s);
+        case 14: return launch_fwd2<6, 3, BIG, true, INJ>(a, n_limbs, mask, s);
+        case 15: return launch_fwd2<7, 4, BIG, true, INJ>(a, n_limbs, mask, s);
+        case 17: return launch_fwd2<9, 5, BIG, true, INJ>(a, n_limbs, mask, s);
 #endif
-        case 16: return launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, 3, s);
+        case 16: return launch_fwd2<8, 4, BIG, true, INJ>(a, n_limbs, mask, s);
     }
     return -1;
 }
 
-int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+// mask: 3 = both passes, 1 / 2 = first / second pass only (N >= 2^12: the caller corrupts the stored intermediate in between)
+int launch_ntt_protected(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s, int mask) {
     if (n_limbs == 0) return 0;
     if (n_limbs > 32768 || a.L == 0 || n_limbs % a.L) return -2;
     if (logn >= 1 && logn <= 11) {
+        if (mask != 3) return -5;
         k_small<false, true><<<n_limbs, 256, sizeof(u64) << logn, s>>>(a, logn);
         return 0;
     }
 #ifdef B200_FAST_BUILD
     if (!big || a.n_inj) return -3;
-    return big == 2 ? launch_prot_t<2, false>(a, logn, n_limbs, s) : launch_prot_t<1, false>(a, logn, n_limbs, s);
+    return big == 2 ? launch_prot_t<2, false>(a, logn, n_limbs, mask, s) : launch_prot_t<1, false>(a, logn, n_limbs, mask, s);
 #else
     // the injection variants exist for the general modes only: NEAR moduli are also valid BIG moduli
-    if (a.n_inj) return big ? launch_prot_t<1, true>(a, logn, n_limbs, s) : launch_prot_t<0, true>(a, logn, n_limbs, s);
-    return big == 2 ? launch_prot_t<2, false>(a, logn, n_limbs, s)
-           : big   ? launch_prot_t<1, false>(a, logn, n_limbs, s) : launch_prot_t<0, false>(a, logn, n_limbs, s);
+    if (a.n_inj) return big ? launch_prot_t<1, true>(a, logn, n_limbs, mask, s) : launch_prot_t<0, true>(a, logn, n_limbs, mask, s);
+    return big == 2 ? launch_prot_t<2, false>(a, logn, n_limbs, mask, s)
+           : big   ? launch_prot_t<1, false>(a, logn, n_limbs, mask, s) : launch_prot_t<0, false>(a, logn, n_limbs, mask, s);
+#endif
+}
+
+template <int BIG>
+static int launch_prot_inv_t(const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+    switch (logn) {
+#ifndef B200_FAST_BUILD
+        case 12: return launch_inv2<4, 4, BIG, true>(a, n_limbs, 3, s);
+        case 13: return launch_inv2<5, 3, BIG, true>(a, n_limbs, 3, s);
+        case 14: return launch_inv2<6, 3, BIG, true>(a, n_limbs, 3, s);
+        case 15: return launch_inv2<7, 4, BIG, true>(a, n_limbs, 3, s);
+        case 17: return launch_inv2<9, 5, BIG, true>(a, n_limbs, 3, s);
+#endif
+        case 16: return launch_inv2<8, 4, BIG, true>(a, n_limbs, 3, s);
+    }
+    return -1;
+}
+
+// protected inverse transform (a.omega / a.abft set, a.tw / a.rtw the INVERSE tables); counters must be zero on entry
+int launch_ntt_protected_inverse(int big, const PassArgs& a, int logn, u32 n_limbs, cudaStream_t s) {
+    if (n_limbs == 0) return 0;
+    if (n_limbs > 32768 || a.L == 0 || n_limbs % a.L) return -2;
+    if (logn >= 1 && logn <= 11) {
+        k_small<true, true><<<n_limbs, 256, sizeof(u64) << logn, s>>>(a, logn);
+        return 0;
+    }
+#ifdef B200_FAST_BUILD
+    if (!big) return -3;
+    return big == 2 ? launch_prot_inv_t<2>(a, logn, n_limbs, s) : launch_prot_inv_t<1>(a, logn, n_limbs, s);
+#else
+    return big == 2 ? launch_prot_inv_t<2>(a, logn, n_limbs, s)
+           : big   ? launch_prot_inv_t<1>(a, logn, n_limbs, s) : launch_prot_inv_t<0>(a, logn, n_limbs, s);
 #endif
 }
 

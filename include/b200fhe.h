@@ -121,7 +121,11 @@ int b200fhe_host_free(void* p);
  * of one butterfly is corrupted before it is used): `stage` in [0, log_n) is the
  * SEAL stage (m = 2^stage groups), `butterfly` in [0, N/2) counts butterflies of
  * that stage in loop order (group-major).  kind 1: v = (v XOR payload) mod q (SBF /
- * DBF, :118-127); kind 2: v = payload mod q (MLF, :128-130). */
+ * DBF, :118-127); kind 2: v = payload mod q (MLF, :128-130).
+ * kind 3 (N >= 2^12): a STORAGE fault -- the SCF class of rfhe_framewk/src/four_step_ntt_protected.cpp:163-196 (SCF-BF one bit,
+ * SCF-MBU 2-4 adjacent bits) at the natural place on a GPU, the intermediate the 2D transform stores to HBM between its two
+ * passes: word `butterfly` (here a coefficient index in [0, N)) of the limb is XOR-ed with `payload` after the first pass has
+ * stored it and before the second pass loads it; `stage` is ignored.  The corrupted word is taken mod q by the second pass. */
 typedef struct b200fhe_inject {
     uint32_t limb;       /* poly * L + l inside the call */
     uint32_t stage;
@@ -150,6 +154,15 @@ int b200fhe_nwt_forward_protected(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_
 /* Host-buffer form: h_verdict [n_poly*L], h_sums optional [n_poly*L][2]. */
 int b200fhe_nwt_forward_protected_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly, size_t L, size_t start_mod,
                                        uint32_t* h_verdict, uint64_t* h_sums, const b200fhe_inject* h_plan, size_t n_plan);
+
+/* The protected INVERSE transform (same identity read backwards; the reference protects only the forward direction, VERDICT r1
+ * asked for both): outputs as b200fhe_nwt_backward; the evaluation-side sum sum_k w^_k a^_k is accumulated on the words the first
+ * pass loads (each taken mod q), the coefficient-side sum sum_i w_i a_i on the values the last pass stores.  d_sums [n_poly*L][2] =
+ * (evaluation side, coefficient side).  No injection plan (defined for the forward transform only). */
+int b200fhe_nwt_backward_protected(b200fhe_ctx* ctx, uint64_t* d_inout, size_t n_poly, size_t L, size_t start_mod,
+                                   uint32_t* d_verdict, uint64_t* d_sums, void* stream);
+int b200fhe_nwt_backward_protected_host(b200fhe_ctx* ctx, uint64_t* h_inout, size_t n_poly, size_t L, size_t start_mod,
+                                        uint32_t* h_verdict, uint64_t* h_sums);
 
 /* The ABFT weights of modulus idx: w[N] (input side) and w_hat[N] (output side, SEAL
  * output order); either pointer may be NULL. */
@@ -390,6 +403,39 @@ int b200fhe_poly_sub(b200fhe_ctx* ctx, uint64_t* d_a, const uint64_t* d_b, size_
 /* The permutation step of rotate_inplace (SEAL apply_galois_ntt): x -> x^galois_elt on n_limbs NTT-form limbs
  * (modulus-independent), galois_elt odd in [1, 2N); out of place. */
 int b200fhe_galois_ntt(b200fhe_ctx* ctx, const uint64_t* d_in, uint64_t* d_out, uint32_t galois_elt, size_t n_limbs, void* stream);
+
+/* ---- BGV host roles + evaluator composition -------------------------------------------------------
+ * What reliability_test/dotprod_test.cu:67-185 obtains from Phantom's classes, behind the C ABI; shim/phantom.h wraps these
+ * in the Phantom names (PhantomContext, PhantomSecretKey, PhantomPublicKey, PhantomBatchEncoder, multiply, ...) so that
+ * dotprod_test.cu / dotprod_real_test.cu / naive_gemm_test.cu compile unmodified.  Ciphertexts are device buffers
+ * [size][n_limbs][N] in NTT form (the layout dotprod_test.cu:42-46 indexes when it flips bits); plaintexts are N host
+ * coefficients mod t.  The object holds the secret key and makes switching keys on first use (fault-injection harness). */
+typedef struct b200fhe_bgv b200fhe_bgv;
+/* EncryptionParameters(scheme_type::bgv) + set_poly_modulus_degree / set_coeff_modulus / set_special_modulus_size /
+ * set_plain_modulus + PhantomContext(parms) (dotprod_test.cu:198-209).  The last special_size moduli are the special primes. */
+int b200fhe_bgv_create(int log_n, const uint64_t* coeff_moduli, int n_moduli, int special_size, uint64_t plain_modulus,
+                       uint64_t seed, int device, b200fhe_bgv** out);
+int b200fhe_bgv_destroy(b200fhe_bgv* h);
+int b200fhe_bgv_info(const b200fhe_bgv* h, int* log_n, int* n_q, int* n_p, uint64_t* plain_modulus, uint64_t* moduli);
+/* PhantomSecretKey(context) (:73), gen_publickey (:74).  gen_relinkey (:75) / create_galois_keys (:143) need no call:
+ * switching keys are generated on first use per level by relinearize / rotate. */
+int b200fhe_bgv_gen_secretkey(b200fhe_bgv* h);
+int b200fhe_bgv_gen_publickey(b200fhe_bgv* h);
+/* PhantomBatchEncoder::encode / decode (:100-101,119,153): SEAL slot order (generator 3). */
+int b200fhe_bgv_encode(b200fhe_bgv* h, const uint64_t* values, size_t n_values, uint64_t* plain /*[N]*/);
+int b200fhe_bgv_decode(b200fhe_bgv* h, const uint64_t* plain, uint64_t* values /*[N]*/);
+/* PhantomPublicKey::encrypt_asymmetric (:105-106): d_ct [2][n_q][N]. */
+int b200fhe_bgv_encrypt(b200fhe_bgv* h, const uint64_t* plain, uint64_t* d_ct);
+/* PhantomSecretKey::decrypt (:118,152): size 2 or 3; `correction` = the ciphertext's correction factor (1 when fresh). */
+int b200fhe_bgv_decrypt(b200fhe_bgv* h, const uint64_t* d_ct, int size, int n_limbs, uint64_t correction, uint64_t* plain);
+/* multiply (:113) -> d_out [3][n_limbs][N]; relinearize_inplace (:114): d_ct [3][..] -> its first two polynomials;
+ * mod_switch_to_next_inplace (:115): -> d_out [size][n_limbs - 1][N], *correction updated; rotate_inplace (:146) by `step`
+ * slots of a row (columns != 0: swap the rows instead); add_inplace (:150). */
+int b200fhe_bgv_multiply(b200fhe_bgv* h, const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, int n_limbs);
+int b200fhe_bgv_relinearize(b200fhe_bgv* h, uint64_t* d_ct, int n_limbs);
+int b200fhe_bgv_mod_switch_to_next(b200fhe_bgv* h, const uint64_t* d_ct, int size, int n_limbs, uint64_t* d_out, uint64_t* correction);
+int b200fhe_bgv_rotate(b200fhe_bgv* h, uint64_t* d_ct, int n_limbs, int step, int columns);
+int b200fhe_bgv_add(b200fhe_bgv* h, uint64_t* d_a, const uint64_t* d_b, int size, int n_limbs);
 
 /* ---- intra-multiplier fold checks of the Barrett multiplier ------------------------
  * rfhe_framewk/src/barrett_final.cpp:120-141 (barrett_reduce_signatures: c, lowK(mul1), lowK(mul2) of one Barrett

@@ -203,3 +203,6 @@ inline void nwt_2d_radix8_backward_inplace(uint64_t* inout, const DNTTTable& ntt
     phantom::detail::check(b200fhe_nwt_backward(ntt_tables.ctx(), inout, 1, coeff_modulus_size, start_modulus_idx, (void*)stream),
                            "nwt_2d_radix8_backward_inplace");
 }
+
+// ---- BGV class surface used by dotprod_test.cu / dotprod_real_test.cu / naive_gemm_test.cu ----
+#include "phantom_bgv.h"

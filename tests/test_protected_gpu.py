@@ -135,3 +135,38 @@ def test_harness_style_input_flip_is_not_flagged(pkg, O):
     assert not verdict.any()
     tabs = [O.Tables(log_n, q) for q in moduli]
     assert np.array_equal(got, O.ntt_forward_batch(a % np.array(moduli, dtype=np.uint64)[:, None], tabs))
+
+
+def test_storage_fault_between_the_passes_is_detected_and_stays_in_its_row(pkg, O):
+    """b200fhe_inject kind 3: the intermediate the column pass stored to HBM is XOR-ed before the row pass loads it (the SCF class of
+    rfhe_framewk/src/four_step_ntt_protected.cpp:163-196 at the 2D transform's round trip).  The checksum trips for that limb
+    only, the damage stays inside the 256 outputs of the row the word belongs to, and the input-side checksum is unchanged."""
+    from fhe_reliability_gpu_b200.binding import fault_payload
+    log_n, L, n_poly = 14, 2, 2
+    N = 1 << log_n
+    moduli = pkg.primes_create(N, [60] * L)
+    ctx = pkg.Context(log_n, moduli)
+    rng = np.random.default_rng(77)
+    a = np.stack([np.stack([rng.integers(0, q, N, dtype=np.uint64) for q in moduli]) for _ in range(n_poly)])
+    clean, v0, s0 = ctx.nwt_forward_protected_host(a.copy())
+    assert not v0.any()
+    for trial, subtype in enumerate(["SCF-BF", "SCF-MBU", "MCF-PPE", "MCF-CTE"] * 3):
+        limb, idx = int(rng.integers(0, n_poly * L)), int(rng.integers(0, N))
+        mask = fault_payload(subtype, 60, rng)
+        out, v, s = ctx.nwt_forward_protected_host(a.copy(), plan=[(limb, 0, idx, 3, mask)])
+        want_v = [0] * (n_poly * L); want_v[limb] = 1
+        assert list(v) == want_v, (subtype, limb, idx, hex(mask))
+        assert (s[:, 0] == s0[:, 0]).all() and s[limb, 1] != s0[limb, 1]
+        diff = (out.reshape(n_poly * L, N) != clean.reshape(n_poly * L, N))
+        row = idx // 256
+        assert diff[limb, row * 256:(row + 1) * 256].any()
+        diff[limb, row * 256:(row + 1) * 256] = False
+        assert not diff.any()
+    # a storage fault together with a butterfly fault in another limb; and the argument checks
+    out, v, _ = ctx.nwt_forward_protected_host(a.copy(), plan=[(0, 0, 17, 3, 1 << 3), (3, 5, 100, 1, 1 << 20)])
+    assert list(v) == [1, 0, 0, 1]
+    with pytest.raises(pkg.B200FHEError):
+        ctx.nwt_forward_protected_host(a.copy(), plan=[(0, 0, N, 3, 1)])
+    small = pkg.Context(6, pkg.primes_create(64, [30]))
+    with pytest.raises(pkg.B200FHEError):
+        small.nwt_forward_protected_host(np.zeros((1, 1, 64), dtype=np.uint64), plan=[(0, 0, 1, 3, 1)])
