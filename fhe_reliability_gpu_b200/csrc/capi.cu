@@ -691,6 +691,7 @@ extern "C" int b200fhe_bconv_destroy(b200fhe_bconv* p) {
     if (p->d_inv) cudaFree(p->d_inv);
     if (p->d_hat) cudaFree(p->d_hat);
     if (p->d_btab) cudaFree(p->d_btab);
+    if (p->d_btab5) cudaFree(p->d_btab5);
     if (p->d_hatw) cudaFree(p->d_hatw);
     if (p->d_ePw) cudaFree(p->d_ePw);
     if (p->d_ePq) cudaFree(p->d_ePq);
@@ -775,6 +776,18 @@ extern "C" int b200fhe_bconv_create_scaled(b200fhe_ctx* c, const int* src_idx, i
                     }
         e = cudaMalloc(&p->d_btab, sizeof(uint2) * bt.size());
         if (e == cudaSuccess) e = cudaMemcpy(p->d_btab, bt.data(), sizeof(uint2) * bt.size(), cudaMemcpyHostToDevice);
+        // the same constants as rows of the tcgen05 B operand: [target][16-byte K chunk kc][digit d] -> bytes (j, a) = (2 kc + b / 8, b % 8)
+        std::vector<uint8_t> b5((size_t)K * 8 * 16 * 16, 0);
+        for (int k = 0; k < K; k++)
+            for (int kc = 0; kc < 8; kc++)
+                for (int d = 0; d < 16; d++)
+                    for (int b = 0; b < 16; b++) {
+                        const int j = 2 * kc + b / 8, a = b % 8, sh = d - a;
+                        if (j < m && sh >= 0 && sh < 8)
+                            b5[(((size_t)k * 8 + kc) * 16 + d) * 16 + b] = (uint8_t)((raw[(size_t)k * m + j] >> (8 * sh)) & 0xff);
+                    }
+        if (e == cudaSuccess) e = cudaMalloc(&p->d_btab5, b5.size());
+        if (e == cudaSuccess) e = cudaMemcpy(p->d_btab5, b5.data(), b5.size(), cudaMemcpyHostToDevice);
     }
     if (e != cudaSuccess) {
         b200fhe_bconv_destroy(p);
@@ -845,7 +858,15 @@ extern "C" int b200fhe_bconv_scale(b200fhe_bconv* p, const uint64_t* d_x, uint64
 extern "C" int b200fhe_bconv_contract(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t k0, size_t kcount, void* stream) {
     if (!p || (kcount && (!d_y || !d_out)) || k0 + kcount > (size_t)p->K) return b200_set_err(B200FHE_EINVAL, "bconv_contract: bad arguments");
     CK(cudaSetDevice(p->ctx->device));
-    int rc;
+    int rc = -1;
+    if (p->d_btab5)
+        rc = launch_bconv_contract_tc5((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, p->d_btab5, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
+                                       (u32)k0, (u32)kcount, (cudaStream_t)stream);
+    if (rc == 0) {
+        if (kcount) g_launches += (kcount + 47) / 48;
+        CK(cudaGetLastError());
+        return 0;
+    }
     if (p->d_btab)
         rc = launch_bconv_contract_tc((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, p->d_btab, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
                                       (u32)k0, (u32)kcount, (cudaStream_t)stream);

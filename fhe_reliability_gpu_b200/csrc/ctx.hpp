@@ -63,6 +63,9 @@ int launch_bconv_exact_fix(const u64* y, u64* out, u32 N, u32 m, u32 K, const u6
 // tensor-core (byte-split, mma.sync u8) contraction for source bases of at most 16 moduli; btab [8][ceil(m/4)][K][8] fragments
 int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint2* btab, u32 N, u32 m, u32 K,
                              u32 k0, u32 kcount, cudaStream_t s);
+// tcgen05 / TMEM contraction (bconv_tc5.cu); returns -1 when the shape is not served there (caller falls back to launch_bconv_contract_tc)
+int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
+                              u32 k0, u32 kcount, cudaStream_t s);
 // checksum-carrying ModUp of one digit (scale + tensor-core contraction + finalize); counters: 6 m + 2 K words of scratch
 int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
                                  const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
@@ -113,6 +116,7 @@ struct b200fhe_bconv {
     ulonglong2* d_inv = nullptr;     // [m] (P/p_j)^-1 mod p_j with Shoup quotient
     u64* d_hat = nullptr;            // [K][m] (P/p_j) mod q_k, 30-bit halves packed
     uint2* d_btab = nullptr;         // m <= 16: the same constants as byte-split tensor-core B fragments (bconv_kernels.cu)
+    uint4* d_btab5 = nullptr;        // m <= 16: the same constants as tcgen05 K-major B rows [K][8][16] x 16 bytes (bconv_tc5.cu)
     int mode = 0;                    // 0: fast (HPS) conversion, 1: exact CRT (motivation/baseConv.py:67-83)
     u64* d_hatw = nullptr;           // exact mode: [m][m] words of P/p_j
     u64* d_ePw = nullptr;            //             [m][m] words of e P, e = 0..m-1
