@@ -92,37 +92,69 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
                      : "memory");
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const u32 row = mt * kT5Rows + quarter * 32 + lane;
+        // one load brings the thread's 64 columns = the 16 digit sums of its four targets; the four recombination + Barrett
+        // chains below are independent, so the scheduler interleaves them (targets past kcount are zero columns: computed, not stored)
+        u32 S[4][16];
+        const u32 ta = tm + ((quarter * 32u) << 16) + buf * 256 + cg * 64;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x64.b32 "
+            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,"
+            "%32,%33,%34,%35,%36,%37,%38,%39,%40,%41,%42,%43,%44,%45,%46,%47,%48,%49,%50,%51,%52,%53,%54,%55,%56,%57,%58,%59,%60,%61,%62,%63}, [%64];"
+            : "=r"(S[0][0]), "=r"(S[0][1]), "=r"(S[0][2]), "=r"(S[0][3]), "=r"(S[0][4]), "=r"(S[0][5]), "=r"(S[0][6]), "=r"(S[0][7]),
+              "=r"(S[0][8]), "=r"(S[0][9]), "=r"(S[0][10]), "=r"(S[0][11]), "=r"(S[0][12]), "=r"(S[0][13]), "=r"(S[0][14]), "=r"(S[0][15]),
+              "=r"(S[1][0]), "=r"(S[1][1]), "=r"(S[1][2]), "=r"(S[1][3]), "=r"(S[1][4]), "=r"(S[1][5]), "=r"(S[1][6]), "=r"(S[1][7]),
+              "=r"(S[1][8]), "=r"(S[1][9]), "=r"(S[1][10]), "=r"(S[1][11]), "=r"(S[1][12]), "=r"(S[1][13]), "=r"(S[1][14]), "=r"(S[1][15]),
+              "=r"(S[2][0]), "=r"(S[2][1]), "=r"(S[2][2]), "=r"(S[2][3]), "=r"(S[2][4]), "=r"(S[2][5]), "=r"(S[2][6]), "=r"(S[2][7]),
+              "=r"(S[2][8]), "=r"(S[2][9]), "=r"(S[2][10]), "=r"(S[2][11]), "=r"(S[2][12]), "=r"(S[2][13]), "=r"(S[2][14]), "=r"(S[2][15]),
+              "=r"(S[3][0]), "=r"(S[3][1]), "=r"(S[3][2]), "=r"(S[3][3]), "=r"(S[3][4]), "=r"(S[3][5]), "=r"(S[3][6]), "=r"(S[3][7]),
+              "=r"(S[3][8]), "=r"(S[3][9]), "=r"(S[3][10]), "=r"(S[3][11]), "=r"(S[3][12]), "=r"(S[3][13]), "=r"(S[3][14]), "=r"(S[3][15])
+            : "r"(ta));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        u64 res[4];
 #pragma unroll
         for (u32 tl = 0; tl < 4; tl++) {
-            const u32 t = c * kT5Chunk + cg * 4 + tl;           // warp-uniform
-            if (t >= kcount) break;
-            u32 S[16];
-            const u32 ta = tm + ((quarter * 32u) << 16) + buf * 256 + (cg * 4 + tl) * 16;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                         : "=r"(S[0]), "=r"(S[1]), "=r"(S[2]), "=r"(S[3]), "=r"(S[4]), "=r"(S[5]), "=r"(S[6]), "=r"(S[7]), "=r"(S[8]), "=r"(S[9]),
-                           "=r"(S[10]), "=r"(S[11]), "=r"(S[12]), "=r"(S[13]), "=r"(S[14]), "=r"(S[15])
-                         : "r"(ta));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            const u32 t = c * kT5Chunk + cg * 4 + tl;
             u64 lo, hi;
-            t5_digits_value(S, lo, hi);
+            t5_digits_value(S[tl], lo, hi);
             const ulonglong4 mk = s.q[t];
-            out[(size_t)t * N + row] = barrett128_raw(lo, hi, mk.x, mk.y, mk.z);
+            res[tl] = barrett128_raw(lo, hi, mk.x, mk.y, mk.z);
+        }
+#pragma unroll
+        for (u32 tl = 0; tl < 4; tl++) {
+            const u32 t = c * kT5Chunk + cg * 4 + tl;
+            if (t < kcount) out[(size_t)t * N + row] = res[tl];
         }
     };
 
-    u32 item = 0, prev_mt = 0, prev_c = 0, tcount = 0;
-    for (u32 mt = blockIdx.x; mt < n_tiles; mt += gridDim.x, tcount++) {
-        unsigned char* A = s.a[tcount & 1];
-        // the tile's y words: row r, limb j -> bytes 8 j .. 8 j + 7 of row r (rows fastest: coalesced 8-byte loads)
-        for (u32 idx = tid; idx < kT5Rows * m; idx += kT5Threads) {
+    // A tile: row r, limb j -> bytes 8 j .. 8 j + 7 of row r (rows fastest: coalesced 8-byte loads).  The NEXT tile's words are
+    // loaded into registers before the epilogues of the current tile and stored into the other buffer after them, so the
+    // global-memory latency hides under the epilogue work.
+    u64 pre[4];
+    auto load_tile = [&](u32 mt) {
+#pragma unroll
+        for (u32 k = 0; k < 4; k++) {
+            const u32 idx = tid + k * kT5Threads;
+            if (idx < kT5Rows * m) pre[k] = __ldg(y + (size_t)(idx >> 7) * N + (size_t)mt * kT5Rows + (idx & (kT5Rows - 1)));
+        }
+    };
+    auto store_tile = [&](unsigned char* A) {
+#pragma unroll
+        for (u32 k = 0; k < 4; k++) {
+            const u32 idx = tid + k * kT5Threads;
             const u32 r = idx & (kT5Rows - 1), j = idx >> 7;
-            const u64 v = __ldg(y + (size_t)j * N + (size_t)mt * kT5Rows + r);
-            *reinterpret_cast<u64*>(A + (j >> 1) * 2048 + r * 16 + (j & 1) * 8) = v;
+            if (idx < kT5Rows * m) *reinterpret_cast<u64*>(A + (j >> 1) * 2048 + r * 16 + (j & 1) * 8) = pre[k];
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy writes -> visible to the tensor core
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    };
+    u32 item = 0, prev_mt = 0, prev_c = 0, tcount = 0;
+    if (blockIdx.x < n_tiles) { load_tile(blockIdx.x); store_tile(s.a[0]); }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    for (u32 mt = blockIdx.x; mt < n_tiles; mt += gridDim.x, tcount++) {
+        unsigned char* A = s.a[tcount & 1];
+        const u32 next = mt + gridDim.x;
+        if (next < n_tiles) load_tile(next);
         for (u32 c = 0; c < nch; c++, item++) {
             if (tid == 0) {
                 const u32 d_tmem = tm + (item & 1) * 256;
@@ -138,7 +170,9 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
             }
             if (item > 0) epilogue(item - 1, prev_mt, prev_c);
             prev_mt = mt; prev_c = c;
-            // the buffer written two items from now is the one just drained: order the tcgen05.ld's before that MMA
+            // the other A buffer's last readers (the previous tile's MMAs) were all waited for by the epilogues above
+            if (c == nch - 1 && next < n_tiles) store_tile(s.a[(tcount + 1) & 1]);
+            // the TMEM buffer written two items from now is the one just drained: order the tcgen05.ld's before that MMA
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncthreads();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
