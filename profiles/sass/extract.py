@@ -6,7 +6,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 LIB = os.path.join(ROOT, "fhe_reliability_gpu_b200", "lib", "libb200fhe.so")
 WANT = {"k_fwd_col": "k_fwd_colILi8ELi4ELi2ELb0ELb0", "k_fwd_col_prot": "k_fwd_colILi8ELi4ELi2ELb1ELb0", "k_fwd_row": "k_fwd_rowILi2ELb0ELb0",
         "k_fwd_row_prot": "k_fwd_rowILi2ELb1ELb0", "k_inv_row": "k_inv_rowILi2E", "k_inv_col": "k_inv_colILi8ELi4ELi2E",
-        "k_bconv_contract_tc": "k_bconv_contract_tcILi4ELb0", "k_pmult": "k_pmult", "k_barrett_fold_checks": "k_barrett_foldILb1ELb1"}
+        "k_bconv_contract_tc": "k_bconv_contract_tcILi4ELb0", "k_bconv_contract_tc5": "k_bconv_contract_tc5", "k_pmult": "k_pmult", "k_barrett_fold_checks": "k_barrett_foldILb1ELb1"}
 txt = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
 funcs = re.split(r"\n\s*Function : ", txt)
 for name, key in WANT.items():
@@ -22,4 +22,4 @@ for name, key in WANT.items():
         f.write("\n# first 60 instructions\n")
         lines = [l for l in body.split("\n") if re.search(r"/\*[0-9a-f]{4}\*/", l)]
         f.write("\n".join(l.rstrip()[:120] for l in lines[:60]) + "\n")
-    print(name, len(ins), {k: cnt[k] for k in cnt if k.startswith(("IMAD.WIDE", "IMAD.HI", "IMMA", "UBLKCP", "SYNCS", "REDUX", "UTMA", "LDGSTS"))})
+    print(name, len(ins), {k: cnt[k] for k in cnt if k.startswith(("IMAD.WIDE", "IMAD.HI", "IMMA", "UBLKCP", "SYNCS", "REDUX", "UTMA", "LDGSTS", "UTC", "LDTM", "DFMA", "DADD"))})
