@@ -84,8 +84,8 @@ def newest_ncu_traffic():
             out = {}
             for name, r, w in zip(rows["Kernel Name"], rows["dram__bytes_read.sum"], rows["dram__bytes_write.sum"]):
                 for k in ("k_fwd_col", "k_fwd_row", "k_inv_row", "k_inv_col"):
-                    if k in name:
-                        out[k] = (float(r) + float(w)) * 1e6      # the summary is in MB; the last (largest-batch) launch wins
+                    if k in name and k not in out:                # the summary is in MB; the first launch of each name = the unprotected kernel
+                        out[k] = (float(r) + float(w)) * 1e6
             if out:
                 return out, os.path.relpath(f, ROOT)
     return {}, None

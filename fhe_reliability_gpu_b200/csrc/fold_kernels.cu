@@ -25,6 +25,7 @@
 #include "../../include/b200fhe.h"
 #include "ctx.hpp"
 #include <vector>
+#include <cstdlib>
 #include <algorithm>
 
 int b200_set_err(int code, const char* fmt, ...);
@@ -80,16 +81,34 @@ __device__ __forceinline__ u32 mulres(u32 x, u32 y, const FoldK& F) {   // x y m
 // ALIGNED: fold is a power of two <= 256 dividing vec_len, so a group never straddles a CTA of 256 threads: its
 // signature / residue sums are reduced in the warp (and across warps through shared memory) and written with plain
 // stores -- no atomics, no clearing pass, the inter comparison done in place.  Otherwise: atomics + k_fold_finish.
-template <bool CHECKS, bool ALIGNED>
+// E: elements per thread.  E = 4 (ALIGNED only, 4 | fold, 4 | n, 16-byte aligned operands): a thread's four consecutive elements
+// belong to one group, so their signatures are combined in registers first -- a quarter of the cross-lane shuffles (the shuffle
+// unit, one warp instruction per cycle per SM, was what bounded the one-element form) and 128-bit loads / stores.
+template <bool CHECKS, bool ALIGNED, int E>
 __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
-    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = i < A.n;
+    static_assert(E == 1 || (E == 4 && ALIGNED), "four elements per thread need the aligned shape");
+    const u64 i0 = ((u64)blockIdx.x * blockDim.x + threadIdx.x) * E;
+    const bool live = i0 < A.n;
     const u64 maskK = A.K >= 64 ? ~0ull : (((u64)1 << A.K) - 1);
     const FoldK F = A.F;
     u64 sig1 = 0, sig2 = 0;
     u32 bad = 0, pred = 0, obs = 0;
+    u64 av[E], bv[E], cv[E];
     if (live) {
-        const u64 t = A.a[i] * A.b[i];                              // barrett_final.cpp:239: u64 ti = a * b
+        if (E == 4) {
+            const ulonglong2 a0 = reinterpret_cast<const ulonglong2*>(A.a + i0)[0], a1 = reinterpret_cast<const ulonglong2*>(A.a + i0)[1];
+            const ulonglong2 b0 = reinterpret_cast<const ulonglong2*>(A.b + i0)[0], b1 = reinterpret_cast<const ulonglong2*>(A.b + i0)[1];
+            av[0] = a0.x; av[1 % E] = a0.y; av[2 % E] = a1.x; av[3 % E] = a1.y;
+            bv[0] = b0.x; bv[1 % E] = b0.y; bv[2 % E] = b1.x; bv[3 % E] = b1.y;
+        } else {
+            av[0] = A.a[i0]; bv[0] = A.b[i0];
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+      const u64 i = i0 + e;
+      if (live) {
+        const u64 t = av[e] * bv[e];                                // barrett_final.cpp:239: u64 ti = a * b
         u64 m1lo = t * A.mu, m1hi = __umul64hi(t, A.mu);            // mul1 = ti * mu (:127)
         u64 c1lo = m1lo;                                            // what the checks see
         const u64 c1hi = m1hi;
@@ -115,9 +134,9 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
         u64 ci = t - m2lo;                                          // (:138-139)
         const u64 cpre = ci;
         if (ci >= A.q) ci -= A.q;
-        A.c[i] = ci;
-        sig1 = (c1lo & maskK) ^ (c2lo & maskK);                     // "instra" (:251-253)
-        sig2 = ci & maskK;                                          // "sum"    (:254-257)
+        cv[e] = ci;
+        sig1 ^= (c1lo & maskK) ^ (c2lo & maskK);                    // "instra" (:251-253)
+        sig2 ^= ci & maskK;                                         // "sum"    (:254-257)
         if (CHECKS) {
             const u32 M = F.M;
             const u32 rt = fold128(t, 0, F);
@@ -129,13 +148,24 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
             u32 rs = fold128(m2lo, 0, F) + fold128(cpre, 0, F);
             if (rs >= M) rs -= M;
             if (m2hi == 0 && m2lo <= t && rs != rt) bad |= 4;
-            pred = p1 + p2; if (pred >= M) pred -= M;
-            obs = r1 + r2; if (obs >= M) obs -= M;
+            pred += p1 + p2;
+            obs += r1 + r2;
         }
+      }
+    }
+    const u64 i = i0;
+    if (live) {
+        if (E == 4) {
+            reinterpret_cast<ulonglong2*>(A.c + i0)[0] = make_ulonglong2(cv[0], cv[1 % E]);
+            reinterpret_cast<ulonglong2*>(A.c + i0)[1] = make_ulonglong2(cv[2 % E], cv[3 % E]);
+        } else {
+            A.c[i0] = cv[0];
+        }
+        if (CHECKS) { pred %= F.M; obs %= F.M; }
     }
     if (ALIGNED) {
-        // n is a multiple of fold and fold divides 256: every group is complete and lives in this CTA
-        const u32 fold = A.fold, lane = threadIdx.x & 31;
+        // n is a multiple of fold and a group (fold / E threads) divides the CTA: every group is complete and lives in this CTA
+        const u32 fold = A.fold / E, lane = threadIdx.x & 31;        // threads per group
         u32 s1l = (u32)sig1, s1h = (u32)(sig1 >> 32), s2l = (u32)sig2, s2h = (u32)(sig2 >> 32);
         const u32 span = fold < 32 ? fold : 32;
         for (u32 o = span >> 1; o; o >>= 1) {
@@ -149,7 +179,7 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
         }
         if (fold <= 32) {
             if (live && (lane & (fold - 1)) == 0) {
-                const u64 g = i / fold;
+                const u64 g = i / A.fold;
                 A.sig_intra[g] = ((u64)s1h << 32) | s1l;
                 A.sig_sum[g] = ((u64)s2h << 32) | s2l;
                 if (CHECKS) A.verdict[g] = bad | (pred % F.M != obs % F.M ? 2u : 0u);
@@ -165,7 +195,7 @@ __global__ void __launch_bounds__(256) k_barrett_fold(FoldArgs A) {
             const u32 wpg = fold >> 5, ngrp = 256 / fold;            // warps per group, groups per CTA
             if (threadIdx.x < ngrp) {
                 const u64 g = ((u64)blockIdx.x * 256) / fold + threadIdx.x;
-                if (g * fold < A.n) {
+                if (g * A.fold < A.n) {
                     u32 v[7] = {0, 0, 0, 0, 0, 0, 0};
                     for (u32 w = threadIdx.x * wpg; w < (threadIdx.x + 1) * wpg; w++) {
                         v[0] ^= sm[w][0]; v[1] ^= sm[w][1]; v[2] ^= sm[w][2]; v[3] ^= sm[w][3];
@@ -271,7 +301,10 @@ extern "C" int b200fhe_barrett_fold(uint64_t q, const uint64_t* d_a, const uint6
     if (checks && (k < 2 || k > 26)) return b200_set_err(B200FHE_EINVAL, "barrett_fold: residue width k must be in [2, 26]");
     if (!d_sig_intra || !d_sig_sum || (checks && !d_verdict)) return b200_set_err(B200FHE_EINVAL, "barrett_fold: null outputs");
     const size_t gpv = (vec_len + fold - 1) / fold, groups = gpv * n_vec;
-    const bool aligned = fold <= 256 && (fold & (fold - 1)) == 0 && vec_len % fold == 0;
+    const bool pow2 = (fold & (fold - 1)) == 0 && vec_len % fold == 0;
+    const bool four = pow2 && fold >= 4 && fold <= 1024 && n % 4 == 0 &&
+                      ((((uintptr_t)d_a) | ((uintptr_t)d_b) | ((uintptr_t)d_c)) & 15) == 0 && !getenv("B200FHE_FOLD_E1");
+    const bool aligned = four || (pow2 && fold <= 256);
     FoldArgs A{};
     A.a = (const u64*)d_a; A.b = (const u64*)d_b; A.c = (u64*)d_c; A.sig_intra = (u64*)d_sig_intra; A.sig_sum = (u64*)d_sig_sum; A.verdict = d_verdict;
     A.n = n; A.vec_len = vec_len; A.groups_per_vec = gpv; A.q = q; A.mu = mu; A.K = (u32)K; A.fold = (u32)fold;
@@ -313,10 +346,13 @@ extern "C" int b200fhe_barrett_fold(uint64_t q, const uint64_t* d_a, const uint6
         A.faults = d_f; A.fault_of = d_of;
     }
     if (e == cudaSuccess) {
-        if (checks && aligned) k_barrett_fold<true, true><<<blocks, 256, 0, s>>>(A);
-        else if (checks) k_barrett_fold<true, false><<<blocks, 256, 0, s>>>(A);
-        else if (aligned) k_barrett_fold<false, true><<<blocks, 256, 0, s>>>(A);
-        else k_barrett_fold<false, false><<<blocks, 256, 0, s>>>(A);
+        const unsigned blocks4 = (unsigned)((n / 4 + 255) / 256);
+        if (checks && four) k_barrett_fold<true, true, 4><<<blocks4, 256, 0, s>>>(A);
+        else if (four) k_barrett_fold<false, true, 4><<<blocks4, 256, 0, s>>>(A);
+        else if (checks && aligned) k_barrett_fold<true, true, 1><<<blocks, 256, 0, s>>>(A);
+        else if (checks) k_barrett_fold<true, false, 1><<<blocks, 256, 0, s>>>(A);
+        else if (aligned) k_barrett_fold<false, true, 1><<<blocks, 256, 0, s>>>(A);
+        else k_barrett_fold<false, false, 1><<<blocks, 256, 0, s>>>(A);
         b200_count_launches(1);
         e = cudaGetLastError();
         if (e == cudaSuccess && checks && !aligned) {
