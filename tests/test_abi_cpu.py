@@ -84,7 +84,7 @@ def test_harness_cli_argument_errors_without_a_gpu():
     dotprod_test.cu:190-194): exit code 1 and the usage / error text, on any machine."""
     import subprocess
     exe = os.path.join(ROOT, "harness", "bin", "ntt_test")
-    dp = os.path.join(ROOT, "harness", "bin", "dotprod_test")
+    dp = os.path.join(ROOT, "harness", "bin", "pmult_fault_test")
     if not (os.path.exists(exe) and os.path.exists(dp)):
         pytest.skip("harness not built (run __graft_entry__.build())")
     p = subprocess.run([exe, "12", "1"], capture_output=True, text=True)

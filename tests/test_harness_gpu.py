@@ -1,4 +1,4 @@
-"""Harness-level parity (SURVEY 8a row a8, 8b iii): the ntt_test / dotprod_test executables keep the
+"""Harness-level parity (SURVEY 8a row a8, 8b iii): the ntt_test / pmult_fault_test executables keep the
 reference's CLI and text contract, and the fault-propagation laws the reference recorded hold.
 
 Contract sources: reliability_test/ntt_test.cu:125-127,171-198 (lines printed),
@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NTT_TEST = os.path.join(ROOT, "harness", "bin", "ntt_test")
-DOTPROD_TEST = os.path.join(ROOT, "harness", "bin", "dotprod_test")
+DOTPROD_TEST = os.path.join(ROOT, "harness", "bin", "pmult_fault_test")
 REF_SHIM = os.path.join(ROOT, "oracle", "_ref", "ntt_test_shim")
 REF_REAL_SHIM = os.path.join(ROOT, "oracle", "_ref", "ntt_real_test_shim")
 
@@ -128,7 +128,7 @@ def test_reference_ntt_real_test_source_on_the_shim():
     assert "ALL CORRECT" in p.stdout
 
 
-def test_dotprod_test_injection_report():
+def test_pmult_fault_test_injection_report():
     p = run(DOTPROD_TEST, 2, 3, 12, 3, 8, 4242)
     assert p.returncode == 0, p.stderr
     inj = re.findall(r"Injected bitflip @ idx=(\d+), bit=(\d+)", p.stderr)          # dotprod_test.cu:57-58
@@ -146,6 +146,6 @@ def test_dotprod_test_injection_report():
     assert ("MISMATCH detected" in p.stdout) == (live > 0)
 
 
-def test_dotprod_test_clean_run_matches():
+def test_pmult_fault_test_clean_run_matches():
     p = run(DOTPROD_TEST, 0, 0, 12, 2, 4, 1)
     assert p.returncode == 0 and "Elementwise symbol errors: 0 / " in p.stdout and "matches" in p.stdout
