@@ -121,6 +121,11 @@ def main():
                                                       stream=torch.cuda.current_stream().cuda_stream), args.steps)
     if int(verdict.abs().sum().item()) != 0:
         raise SystemExit("protected key-switch flagged a fault-free run")
+    vntt = torch.zeros(ks.ntt_count(), dtype=torch.int32, device="cuda")
+    ms_full = timed(torch, lambda: ks.apply_protected_full(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr(), verdict.data_ptr(),
+                                                           vntt.data_ptr(), stream=torch.cuda.current_stream().cuda_stream), args.steps)
+    if int(verdict.abs().sum().item()) != 0 or int(vntt.abs().sum().item()) != 0:
+        raise SystemExit("fully protected key-switch flagged a fault-free run")
     # pieces (eager)
     d_up = torch.zeros((dnum, total, N), dtype=torch.int64, device="cuda")
     accq = torch.zeros((2, n_q, N), dtype=torch.int64, device="cuda")
@@ -173,6 +178,9 @@ def main():
         "config": {"workload": "f1: hybrid key-switch, N=2^%d, %d ciphertext limbs + %d special primes, dnum=%d, 60-bit" % (log_n, n_q, n_p, dnum)},
         "checksum_carrying_conversions": {"ms_eager": ms_prot, "overhead_pct_vs_eager": 100.0 * (ms_prot / ms_eager - 1.0),
                                           "checks": (dnum + 2) * total},
+        "fully_protected": {"ms_eager": ms_full, "overhead_pct_vs_eager": 100.0 * (ms_full / ms_eager - 1.0),
+                            "checks": (dnum + 2) * total + int(vntt.numel()),
+                            "note": "conversion checks + one fused-checksum verdict per limb-transform (b200fhe_keyswitch_apply_protected_full)"},
         "pieces_ms": {"modup": ms_up, "evk_inner_product": ms_ip, "moddown": ms_down},
         "work_per_step": {"limb_transforms": transforms, "bconv_mulmods": mulmods, "algorithmic_bytes": words * 8},
         "roofline": {"bound": "integer multiplier pipe (NTT butterflies + dense base-conversion contraction); HBM shown for scale",

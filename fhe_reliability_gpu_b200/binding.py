@@ -64,6 +64,8 @@ SIGNATURES = {
     "b200fhe_keyswitch_moddown": (i32, [vp, vp, vp, vp, sz, vp]),
     "b200fhe_keyswitch_apply": (i32, [vp, vp, vp, vp, vp, vp]),
     "b200fhe_keyswitch_apply_protected": (i32, [vp, vp, vp, vp, vp, vp, vp]),
+    "b200fhe_keyswitch_apply_protected_full": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
+    "b200fhe_keyswitch_ntt_count": (i32, [vp, C.POINTER(sz)]),
     "b200fhe_keyswitch_set_inject": (i32, [vp, i32, vp, sz]),
     "b200fhe_shard_unique_id": (i32, [C.POINTER(C.c_uint8)]),
     "b200fhe_shard_init": (i32, [vp, i32, i32, C.POINTER(vp)]),
@@ -409,6 +411,21 @@ class KeySwitch:
     def apply_protected(self, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, verdict_ptr, stream=0):
         """verdict: uint32 [dnum + 2][n_q + n_p] on the device; all zero = every conversion check passed."""
         check(lib().b200fhe_keyswitch_apply_protected(self._h, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, verdict_ptr, stream))
+
+
+def _ks_ntt_count(self):
+    n = sz()
+    check(lib().b200fhe_keyswitch_ntt_count(self._h, C.byref(n)))
+    return int(n.value)
+
+
+def _ks_apply_protected_full(self, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, verdict_ptr, verdict_ntt_ptr, stream=0):
+    """apply_protected with every limb-transform protected too; verdict_ntt: uint32 [ntt_count()] on the device."""
+    check(lib().b200fhe_keyswitch_apply_protected_full(self._h, c_ptr, evk_q_ptr, evk_p_ptr, out_ptr, verdict_ptr, verdict_ntt_ptr, stream))
+
+
+KeySwitch.ntt_count = _ks_ntt_count
+KeySwitch.apply_protected_full = _ks_apply_protected_full
 
 
 def flip_bit(ptr, idx, bit, stream=0):

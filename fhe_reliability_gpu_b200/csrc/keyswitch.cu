@@ -188,7 +188,9 @@ int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uin
 
 // verdict (optional): [dnum][n_q + n_p] checksum verdicts of the digits' conversions (b200fhe_bconv_modup_protected layout:
 // alpha source-limb entries, then the targets)
-static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, uint32_t* verdict, void* stream) {
+// vntt (optional, only with verdict): per-limb verdicts of the protected transforms, in launch order: INTT(c) [n_q], then per digit
+// its targets below [d alpha] and above [total - (d + 1) alpha]
+static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, uint32_t* verdict, void* stream, uint32_t* vntt = nullptr) {
     if (!k || !d_c || !d_up) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: null argument");
     if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
@@ -204,7 +206,8 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
                            cudaMemcpyDeviceToDevice, s));
     // unprotected: the inverse NTT's final constant carries the conversion's scale step, so x already IS y = x (D/q_j)^-1;
     // protected: plain inverse NTT, the scale step runs as its own checked kernel
-    if (verdict) RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
+    if (verdict && vntt) { RC(b200fhe_nwt_backward_protected(c, x, 1, (size_t)k->n_q, 0, vntt, nullptr, stream)); vntt += k->n_q; }
+    else if (verdict) RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
     else RC(b200_nwt_backward_mods(c, x, 1, (size_t)k->n_q, 0, k->d_mods_scaled, stream));
     for (int d = 0; d < k->dnum; d++) {
         b200fhe_bconv* p = k->up[d];
@@ -220,8 +223,14 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
             RC(b200fhe_bconv_contract(p, xd, upd, 0, below, stream));
             RC(b200fhe_bconv_contract(p, xd, upd + (below + a) * N, below, above, stream));
         }
-        if (below) RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
-        RC(b200fhe_nwt_forward(c, upd + (below + a) * N, 1, above, below + a, stream));
+        if (vntt) {
+            if (below) RC(b200fhe_nwt_forward_protected(c, upd, 1, below, 0, vntt, nullptr, nullptr, 0, stream));
+            RC(b200fhe_nwt_forward_protected(c, upd + (below + a) * N, 1, above, below + a, vntt + below, nullptr, nullptr, 0, stream));
+            vntt += below + above;
+        } else {
+            if (below) RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
+            RC(b200fhe_nwt_forward(c, upd + (below + a) * N, 1, above, below + a, stream));
+        }
     }
     return 0;
 }
@@ -233,7 +242,7 @@ extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c
 // step 4 for n_poly polynomials: d_acc_q [n_poly][n_q][N], d_acc_p [n_poly][n_p][N] (overwritten), d_out [n_poly][n_q][N]
 // (may alias d_acc_q).  n_poly <= 2.
 static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out, size_t n_poly,
-                        uint32_t* verdict /*optional [n_poly][n_p + n_q]*/, void* stream) {
+                        uint32_t* verdict /*optional [n_poly][n_p + n_q]*/, void* stream, uint32_t* vntt = nullptr /*[n_poly n_p] then [n_poly n_q]*/) {
     if (!k || !d_acc_q || !d_acc_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: null argument");
     if (n_poly < 1 || n_poly > 2) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: n_poly must be 1 or 2");
     b200fhe_ctx* c = k->ctx;
@@ -242,7 +251,8 @@ static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t*
     const size_t N = c->N, nq = (size_t)k->n_q, np = (size_t)k->n_p;
     uint64_t* y = k->d_ws + k->o_y;
     uint64_t* conv = k->d_ws + k->o_conv;
-    if (verdict) RC(b200fhe_nwt_backward(c, d_acc_p, n_poly, np, nq, stream));
+    if (verdict && vntt) RC(b200fhe_nwt_backward_protected(c, d_acc_p, n_poly, np, nq, vntt, nullptr, stream));
+    else if (verdict) RC(b200fhe_nwt_backward(c, d_acc_p, n_poly, np, nq, stream));
     else RC(b200_nwt_backward_mods(c, d_acc_p, n_poly, np, nq, k->d_mods_scaled, stream));     // scale step folded in: acc_p is y
     for (size_t p = 0; p < n_poly; p++) {
         if (verdict) {
@@ -253,7 +263,8 @@ static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t*
             RC(b200fhe_bconv_contract(k->down, d_acc_p + p * np * N, conv + p * nq * N, 0, nq, stream));
         }
     }
-    RC(b200fhe_nwt_forward(c, conv, n_poly, nq, 0, stream));
+    if (verdict && vntt) RC(b200fhe_nwt_forward_protected(c, conv, n_poly, nq, 0, vntt + n_poly * np, nullptr, nullptr, 0, stream));
+    else RC(b200fhe_nwt_forward(c, conv, n_poly, nq, 0, stream));
     dim3 grid((unsigned)((N / 2 + 255) / 256), (unsigned)nq, (unsigned)n_poly);
     k_moddown_combine<<<grid, 256, 0, s>>>((const u64*)d_acc_q, (const u64*)conv, (u64*)d_out, c->d_mods, k->d_pinv, (u32)N, (u32)nq);
     b200_count_launches(1);
@@ -268,8 +279,9 @@ extern "C" int b200fhe_keyswitch_moddown(b200fhe_keyswitch* k, const uint64_t* d
 
 // The whole switch: d_c [n_q][N]; d_evk_q [dnum][2][n_q][N]; d_evk_p [dnum][2][n_p][N]; d_out [2][n_q][N].
 // out[0] + out[1] s  ~  c s'   when evk_d = (-a_d s + e_d + P B_d s', a_d) with B_d the CRT basis element of digit d.
+static size_t modup_ntt_count(const b200fhe_keyswitch* k) { return (size_t)k->n_q + (size_t)k->dnum * ((size_t)k->n_q + k->n_p - k->alpha); }
 static int apply_impl(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p, uint64_t* d_out,
-                      uint32_t* verdict, void* stream) {
+                      uint32_t* verdict, void* stream, uint32_t* vntt = nullptr) {
     if (!k || !d_c || !d_evk_q || !d_evk_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: null argument");
     if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
@@ -277,13 +289,13 @@ static int apply_impl(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t*
     uint64_t* up = k->d_ws + k->o_up;
     uint64_t* accq = k->d_ws + k->o_accq;
     uint64_t* accp = k->d_ws + k->o_accp;
-    RC(modup_impl(k, d_c, up, verdict, stream));
+    RC(modup_impl(k, d_c, up, verdict, stream, vntt));
     std::vector<const uint64_t*> ct(k->dnum), pt(k->dnum);
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
     RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accq, 2, nq, 0, 0, stream));
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_p + (size_t)d * 2 * np * N; pt[d] = up + ((size_t)d * total + nq) * N; }
     RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accp, 2, np, nq, 0, stream));
-    return moddown_impl(k, accq, accp, d_out, 2, verdict ? verdict + (size_t)k->dnum * total : nullptr, stream);
+    return moddown_impl(k, accq, accp, d_out, 2, verdict ? verdict + (size_t)k->dnum * total : nullptr, stream, vntt ? vntt + modup_ntt_count(k) : nullptr);
 }
 
 extern "C" int b200fhe_keyswitch_apply(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
@@ -301,6 +313,23 @@ extern "C" int b200fhe_keyswitch_apply_protected(b200fhe_keyswitch* k, const uin
     int rc = apply_impl(k, d_c, d_evk_q, d_evk_p, d_out, d_verdict, stream);
     if (k) { k->inj_conv = -1; k->inj.clear(); }              // an armed injection is consumed by one call
     return rc;
+}
+
+// The same, with EVERY limb-transform of the switch protected as well (b200fhe_nwt_forward_protected / _backward_protected): the
+// 320 transforms at C5's shape are 48 % of a switch's cost by the reference's own split (profile_framewk/draw_dnum.py:5-9).
+// d_verdict_ntt [b200fhe_keyswitch_ntt_count]: INTT(c) [n_q]; per digit its targets below then above the digit; ModDown's INTT of the
+// P part [2 n_p] and NTT of the converted part [2 n_q].  All zero = no transform's checksum tripped.
+extern "C" int b200fhe_keyswitch_apply_protected_full(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                                                      uint64_t* d_out, uint32_t* d_verdict, uint32_t* d_verdict_ntt, void* stream) {
+    if (!d_verdict || !d_verdict_ntt) return b200_set_err(B200FHE_EINVAL, "keyswitch_apply_protected_full: null verdict");
+    int rc = apply_impl(k, d_c, d_evk_q, d_evk_p, d_out, d_verdict, stream, d_verdict_ntt);
+    if (k) { k->inj_conv = -1; k->inj.clear(); }
+    return rc;
+}
+extern "C" int b200fhe_keyswitch_ntt_count(const b200fhe_keyswitch* k, size_t* n) {
+    if (!k || !n || !k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_ntt_count: needs a full key-switch plan");
+    *n = modup_ntt_count(k) + 2 * (size_t)k->n_p + 2 * (size_t)k->n_q;
+    return 0;
 }
 
 // Arms faults for the NEXT b200fhe_keyswitch_apply_protected: `conversion` in [0, dnum) = that digit's ModUp conversion,

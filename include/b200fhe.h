@@ -343,6 +343,14 @@ int b200fhe_keyswitch_apply(b200fhe_keyswitch* plan, const uint64_t* d_c, const 
 int b200fhe_keyswitch_apply_protected(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
                                       uint64_t* d_out, uint32_t* d_verdict, void* stream);
 
+/* The same switch with every limb-transform protected too (the fused-checksum forward / inverse NTT): d_verdict_ntt
+ * [b200fhe_keyswitch_ntt_count] in launch order -- INTT(c) [n_q]; per digit its target limbs below, then above the digit; ModDown's
+ * INTT of the P part [2][n_p] and NTT of the converted part [2][n_q].  320 transforms at N=2^17, 48 + 16, dnum = 3: the 48 % of a
+ * switch that profile_framewk/draw_dnum.py:5-9 attributes to the NTT.  Same output bits as b200fhe_keyswitch_apply. */
+int b200fhe_keyswitch_apply_protected_full(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
+                                           uint64_t* d_out, uint32_t* d_verdict, uint32_t* d_verdict_ntt, void* stream);
+int b200fhe_keyswitch_ntt_count(const b200fhe_keyswitch* plan, size_t* n);
+
 /* Fault injection for the NEXT b200fhe_keyswitch_apply_protected (consumed by it): `conversion` in [0, dnum) = that digit's
  * ModUp conversion, dnum / dnum + 1 = the ModDown conversion of out[0] / out[1]; entries as in b200fhe_bconv_modup_protected. */
 int b200fhe_keyswitch_set_inject(b200fhe_keyswitch* plan, int conversion, const b200fhe_bconv_inject* inject, size_t n_inject);

@@ -175,3 +175,36 @@ def test_protected_keyswitch_flags_the_faulty_conversion(pkg, O, conversion, inj
     ks.apply_protected(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), out.data_ptr(), verdict.data_ptr())
     torch.cuda.synchronize()
     assert int(verdict.abs().sum().item()) == 0 and torch.equal(out, clean)      # the injection was consumed
+
+
+@pytest.mark.parametrize("log_n,n_q,n_p,dnum", [(10, 6, 2, 3), (12, 8, 4, 2), (17, 48, 16, 3)])
+def test_fully_protected_keyswitch_also_checks_every_transform(pkg, O, log_n, n_q, n_p, dnum):
+    """apply_protected_full: the conversions' checks plus one fused-checksum verdict per limb-transform of the switch (INTT(c), the
+    digits' NTTs, ModDown's INTT / NTT): same output bits, all verdicts clean; a fault injected into one conversion trips that
+    conversion's check and NONE of the transform checks (the transforms faithfully transform the corrupted data: faults are located)."""
+    import torch
+    N, moduli, ctx, tabs = _setup(pkg, O, log_n, n_q, n_p)
+    ks = pkg.KeySwitch(ctx, n_q, n_p, dnum)
+    total, alpha = n_q + n_p, n_q // dnum
+    n_ntt = ks.ntt_count()
+    assert n_ntt == n_q + dnum * (total - alpha) + 2 * n_p + 2 * n_q
+    g = torch.Generator(device="cuda").manual_seed(log_n + 100)
+    c = torch.randint(0, 1 << 59, (n_q, N), dtype=torch.int64, device="cuda", generator=g)
+    eq = torch.randint(0, 1 << 59, (dnum, 2, n_q, N), dtype=torch.int64, device="cuda", generator=g)
+    ep = torch.randint(0, 1 << 59, (dnum, 2, n_p, N), dtype=torch.int64, device="cuda", generator=g)
+    out = torch.zeros((2, n_q, N), dtype=torch.int64, device="cuda")
+    outp = torch.zeros_like(out)
+    ks.apply(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), out.data_ptr())
+    for _ in range(2):
+        vc = torch.full((dnum + 2, total), 7, dtype=torch.int32, device="cuda")
+        vn = torch.full((n_ntt,), 7, dtype=torch.int32, device="cuda")
+        ks.apply_protected_full(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), outp.data_ptr(), vc.data_ptr(), vn.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.equal(out, outp)
+        assert int(vc.abs().sum().item()) == 0 and int(vn.abs().sum().item()) == 0
+    ks.set_inject(dnum, [(2, 1, 3, 1 << 9)])                    # ModDown of out[0]: one contraction output
+    vc.fill_(7); vn.fill_(7)
+    ks.apply_protected_full(c.data_ptr(), eq.data_ptr(), ep.data_ptr(), outp.data_ptr(), vc.data_ptr(), vn.data_ptr())
+    torch.cuda.synchronize()
+    assert int(vc[dnum, n_p + 1].item()) != 0 and int((vc != 0).sum().item()) == 1
+    assert int(vn.abs().sum().item()) == 0 and not torch.equal(out, outp)
