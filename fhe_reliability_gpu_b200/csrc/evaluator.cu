@@ -30,12 +30,15 @@ __global__ void __launch_bounds__(256) k_ct_tensor(const u64* __restrict__ a, co
     const size_t off = ((size_t)limb * N) / 2 + i2, poly2 = ((size_t)L * N) / 2;
     const ulonglong2 a0 = __ldcs(reinterpret_cast<const ulonglong2*>(a) + off), a1 = __ldcs(reinterpret_cast<const ulonglong2*>(a) + poly2 + off);
     const ulonglong2 b0 = __ldcs(reinterpret_cast<const ulonglong2*>(b) + off), b1 = __ldcs(reinterpret_cast<const ulonglong2*>(b) + poly2 + off);
-    auto mul = [&](u64 x, u64 y) { return barrett128(x * y, __umul64hi(x, y), m); };
-    auto mul2 = [&](u64 x0, u64 y0, u64 x1, u64 y1) {          // x0 y0 + x1 y1 mod q with one reduction (192-bit sum)
+    // reduce128: three folds of 2^bits = delta for the pseudo-Mersenne primes and in-range operands (the usual case: 5 IMAD.WIDE
+    // instead of a 128-bit Barrett's ~17 -- this streaming kernel was multiplier-bound at 51 % of the HBM peak), Barrett otherwise
+    auto mul = [&](u64 x, u64 y) { return reduce128(x * y, __umul64hi(x, y), m); };
+    auto mul2 = [&](u64 x0, u64 y0, u64 x1, u64 y1) {          // x0 y0 + x1 y1 mod q with one reduction
         const u64 l0 = x0 * y0, h0 = __umul64hi(x0, y0), l1 = x1 * y1, h1 = __umul64hi(x1, y1);
         const u64 lo = l0 + l1, c = lo < l0;
         const u64 t = h0 + h1, hi = t + c;
         const u64 top = (u64)(t < h0) + (u64)(hi < t);         // carry out of the high word (0 or 1)
+        if (top == 0) return reduce128(lo, hi, m);             // operands below q: the sum is below 2 q^2
         const u64 r1 = barrett128(hi, top, m);                 // (top:hi) mod q
         return barrett128(lo, r1, m);
     };

@@ -187,6 +187,42 @@ __device__ __forceinline__ u64 mulmod_barrett(u64 a, u64 b, const B200Mod& m) {
     return barrett128(a * b, __umul64hi(a, b), m);
 }
 
+// (hi:lo) < 2^(2 bits + 4) modulo a pseudo-Mersenne q = 2^bits - delta (50 <= bits <= 60, delta < 2^31: the shape of every prime
+// CoeffModulus::Create hands out) by folding 2^bits = delta three times -- 5 IMAD.WIDE against the ~17 of barrett128:
+//   V1 = (V  >> bits) delta + (V  mod 2^bits) < 2^(bits + 35) + 2^bits
+//   V2 = (V1 >> bits) delta + (V1 mod 2^bits) < 2^66 + 2^bits
+//   V3 = (V2 >> bits) delta + (V2 mod 2^bits) < 2^(97 - bits) + 2^bits < 2 q      -> one conditional subtraction.  Result in [0,q).
+// One long dependent chain: pays in throughput-bound streaming kernels, not in latency-bound ones (profiles/r2r_tc5_nearfold.txt).
+__device__ __forceinline__ u64 fold128_near(u64 lo, u64 hi, u64 q, u32 delta, u32 bits) {
+    const u64 mask = ((u64)1 << bits) - 1;
+    const u64 h1 = (lo >> bits) | (hi << (64 - bits));
+    u64 p0, p1;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(p0) : "r"((u32)h1), "r"(delta));
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(p1) : "r"((u32)(h1 >> 32)), "r"(delta));
+    u64 v1lo = p0 + (p1 << 32);
+    u64 v1hi = (p1 >> 32) + (v1lo < p0);
+    const u64 l1 = lo & mask;
+    v1lo += l1;
+    v1hi += (v1lo < l1);
+    const u64 h2 = (v1lo >> bits) | (v1hi << (64 - bits));
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(p0) : "r"((u32)h2), "r"(delta));
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(p1) : "r"((u32)(h2 >> 32)), "r"(delta));
+    u64 v2lo = p0 + (p1 << 32);
+    u64 v2hi = (p1 >> 32) + (v2lo < p0);
+    const u64 l2 = v1lo & mask;
+    v2lo += l2;
+    v2hi += (v2lo < l2);
+    const u32 h3 = (u32)((v2lo >> bits) | (v2hi << (64 - bits)));
+    u64 v3;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(v3) : "r"(h3), "r"(delta), "l"(v2lo & mask));
+    return v3 >= q ? v3 - q : v3;
+}
+// (hi:lo) mod q: the fold when the modulus has the shape and the value is in its range, the general Barrett otherwise
+__device__ __forceinline__ u64 reduce128(u64 lo, u64 hi, const B200Mod& m) {
+    if (m.near && m.bits >= 50 && (hi >> (2 * m.bits - 60)) == 0) return fold128_near(lo, hi, m.q, m.delta, m.bits);
+    return barrett128(lo, hi, m);
+}
+
 __device__ __forceinline__ ulonglong2 ldg_tw(const ulonglong2* p) {
     return __ldg(p);
 }
