@@ -40,15 +40,7 @@ __global__ void __launch_bounds__(256) k_bconv_scale(const u64* __restrict__ x, 
 //   in between: the y sums at the producer's store equal the y sums at the consumer's load (memory / transfer fault)
 // Sums are exact integers kept as separate sums of the low and high 32-bit halves (each < 2^32 N); reduction mod the
 // moduli happens once, in k_bconv_prot_finalize.
-struct BconvInj {          // device copy of b200fhe_bconv_inject
-    u32 stage, limb;
-    u64 coeff, mask;
-};
-constexpr int kBconvMaxInj = 8;
-struct BconvInjList {
-    BconvInj e[kBconvMaxInj];
-    u32 n;
-};
+// BconvInj / BconvInjList (device copy of b200fhe_bconv_inject): ctx.hpp, shared with bconv_tc5.cu
 
 __device__ __forceinline__ u64 warp_sum64(u64 v) {
 #pragma unroll
@@ -490,7 +482,7 @@ __global__ void k_bconv_xor(u64* y, size_t idx, u64 mask) { y[idx] ^= mask; }
 int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
                                  const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
                                  u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches,
-                                 u64* out_hi, u32 k_split) {
+                                 u64* out_hi, u32 k_split, const uint4* btab5) {
     if (!btab || m > 16 || n_inj > (u32)kBconvMaxInj) return -1;
     BconvInjList il;
     il.n = n_inj;
@@ -505,13 +497,18 @@ int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* 
         }
     u64* cin = counters + (size_t)4 * m;
     u64* cout = counters + (size_t)6 * m;
+    // tcgen05 contraction first (bconv_tc5.cu); the mma.sync kernel serves the shapes it declines
+    auto contract = [&](u64* o, u32 k0, u32 kcount, u64* ci) {
+        if (launch_bconv_contract_tc5_prot(y, o, mods, dst_idx, btab5, N, m, K, k0, kcount, s, ci, cout, il) == 0) return 0;
+        return launch_tc_ks<true>(y, o, mods, dst_idx, btab, N, m, K, k0, kcount, s, ci, cout, il);
+    };
     int rc;
     if (out_hi && k_split < K) {
-        rc = k_split ? launch_tc_ks<true>(y, out, mods, dst_idx, btab, N, m, K, 0, k_split, s, cin, cout, il) : 0;
-        if (!rc) rc = launch_tc_ks<true>(y, out_hi, mods, dst_idx, btab, N, m, K, k_split, K - k_split, s, k_split ? nullptr : cin, cout, il);
+        rc = k_split ? contract(out, 0, k_split, cin) : 0;
+        if (!rc) rc = contract(out_hi, k_split, K - k_split, k_split ? nullptr : cin);
         nl += k_split ? 1 : 0;
     } else {
-        rc = launch_tc_ks<true>(y, out, mods, dst_idx, btab, N, m, K, 0, K, s, cin, cout, il);
+        rc = contract(out, 0, K, cin);
     }
     if (rc) return rc;
     k_bconv_prot_finalize<<<(m + K + 3) / 4, 128, 0, s>>>(counters, next_counters, mods, src_idx, dst_idx, inv, hat, m, K, verdict, sums);

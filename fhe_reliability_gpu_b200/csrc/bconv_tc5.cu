@@ -41,17 +41,25 @@ __device__ __forceinline__ void t5_digits_value(const u32 (&S)[16], u64& lo, u64
     hi = (W[1] >> 32) + W[2] + (W[3] << 32) + (lo < W[0]);
 }
 
+__device__ __forceinline__ void t5_red_add64(u64* p, u64 v) { asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+
 struct T5Smem {
     unsigned char a[2][kT5ABytes];
     unsigned char b[kT5MaxChunks][kT5BBytes];
     ulonglong4 q[kT5MaxChunks * kT5Chunk];
     u64 bar[2];
     u32 tmem;
+    u64 so[kT5Threads / 32][kT5MaxChunks][8];      // PROT: per-warp output sums, [4 targets of the warp][low / high half]
 };
 
+// PROT (checksum-carrying flavour): cin [m][2] += sums of the low / high 32-bit halves of the y words as this
+// kernel loads them (nullptr: not this launch), cout [K][2] += the same sums of the outputs as stored; stage-2 faults of `inj` are
+// XORed into the stored (and summed) outputs.  The sums ride on data already in registers: no extra pass over memory.
+template <bool PROT>
 __global__ void __launch_bounds__(kT5Threads, 1)
 k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B200Mod* mods, const u32* dst_idx,
-                     const uint4* __restrict__ btab5 /*[K][8][16] 16-byte entries*/, u32 N, u32 m, u32 k0, u32 kcount) {
+                     const uint4* __restrict__ btab5 /*[K][8][16] 16-byte entries*/, u32 N, u32 m, u32 k0, u32 kcount, u64* cin, u64* cout,
+                     const __grid_constant__ BconvInjList inj) {
     extern __shared__ __align__(1024) unsigned char smraw[];
     T5Smem& s = *reinterpret_cast<T5Smem*>(smraw);
     const u32 tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -68,6 +76,8 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
         const B200Mod& mk = mods[dst_idx[k0 + (t < kcount ? t : kcount - 1)]];
         s.q[t] = make_ulonglong4(mk.q, mk.ratio0, mk.ratio1, 0);
     }
+    if (PROT)
+        for (u32 k = tid; k < (kT5Threads / 32) * kT5MaxChunks * 8; k += kT5Threads) (&s.so[0][0][0])[k] = 0;
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(t5_smem(&s.bar[0])));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(t5_smem(&s.bar[1])));
@@ -119,6 +129,34 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
             const ulonglong4 mk = s.q[t];
             res[tl] = barrett128_raw(lo, hi, mk.x, mk.y, mk.z);
         }
+        if (PROT) {
+            for (u32 e = 0; e < inj.n; e++)                       // a faulty reduction: the corrupted output is stored AND summed
+                if (inj.e[e].stage == 2 && inj.e[e].coeff == row) {
+#pragma unroll
+                    for (u32 tl = 0; tl < 4; tl++)
+                        if (inj.e[e].limb == k0 + c * kT5Chunk + cg * 4 + tl) res[tl] ^= inj.e[e].mask;
+                }
+            // sums over the warp's 32 rows of the 8 values (4 targets x 2 halves), transposing while reducing: each round halves
+            // the values a lane carries, 4 + 2 + 1 + 1 + 1 = 9 64-bit shuffles instead of 8 x 5
+            u64 v[8];
+#pragma unroll
+            for (u32 tl = 0; tl < 4; tl++) {
+                const bool live = c * kT5Chunk + cg * 4 + tl < kcount;
+                v[2 * tl] = live ? (res[tl] & 0xffffffffull) : 0;
+                v[2 * tl + 1] = live ? (res[tl] >> 32) : 0;
+            }
+            const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+            u64 w[4], x[2];
+#pragma unroll
+            for (int i = 0; i < 4; i++) w[i] = (b4 ? v[i + 4] : v[i]) + __shfl_xor_sync(0xffffffffu, b4 ? v[i] : v[i + 4], 16);
+#pragma unroll
+            for (int i = 0; i < 2; i++) x[i] = (b3 ? w[i + 2] : w[i]) + __shfl_xor_sync(0xffffffffu, b3 ? w[i] : w[i + 2], 8);
+            u64 z = (b2 ? x[1] : x[0]) + __shfl_xor_sync(0xffffffffu, b2 ? x[0] : x[1], 4);
+            z += __shfl_xor_sync(0xffffffffu, z, 2);
+            z += __shfl_xor_sync(0xffffffffu, z, 1);
+            // lane 4 e now holds value e = bit2 + 2 bit3 + 4 bit4 of the lane index: one lane per entry, plain read-add-write
+            if ((lane & 3) == 0) s.so[warp][c][lane >> 2] += z;
+        }
 #pragma unroll
         for (u32 tl = 0; tl < 4; tl++) {
             const u32 t = c * kT5Chunk + cg * 4 + tl;
@@ -130,11 +168,15 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
     // loaded into registers before the epilogues of the current tile and stored into the other buffer after them, so the
     // global-memory latency hides under the epilogue work.
     u64 pre[4];
+    u64 ci[4][2] = {};                                        // PROT: this thread's y sums; word k of a thread is always limb (tid >> 7) + 4 k
     auto load_tile = [&](u32 mt) {
 #pragma unroll
         for (u32 k = 0; k < 4; k++) {
             const u32 idx = tid + k * kT5Threads;
-            if (idx < kT5Rows * m) pre[k] = __ldg(y + (size_t)(idx >> 7) * N + (size_t)mt * kT5Rows + (idx & (kT5Rows - 1)));
+            if (idx < kT5Rows * m) {
+                pre[k] = __ldg(y + (size_t)(idx >> 7) * N + (size_t)mt * kT5Rows + (idx & (kT5Rows - 1)));
+                if (PROT) { ci[k][0] += pre[k] & 0xffffffffull; ci[k][1] += pre[k] >> 32; }
+            }
         }
     };
     auto store_tile = [&](unsigned char* A) {
@@ -181,12 +223,33 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
     if (item > 0) epilogue(item - 1, prev_mt, prev_c);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (PROT) {
+        // outputs: entry (c, cg, e) summed over the four row quarters (warps cg * 4 .. cg * 4 + 3), one global reduction per CTA and entry
+        for (u32 k = tid; k < nch * 32; k += kT5Threads) {
+            const u32 c = k >> 5, g4 = (k >> 3) & 3, e = k & 7, t = c * kT5Chunk + g4 * 4 + (e >> 1);
+            const u64 v = s.so[g4 * 4][c][e] + s.so[g4 * 4 + 1][c][e] + s.so[g4 * 4 + 2][c][e] + s.so[g4 * 4 + 3][c][e];
+            if (t < kcount) t5_red_add64(cout + (size_t)(k0 + t) * 2 + (e & 1), v);
+        }
+        if (cin) {
+#pragma unroll
+            for (u32 k = 0; k < 4; k++)
+#pragma unroll
+                for (u32 h = 0; h < 2; h++) {
+                    u64 v = ci[k][h];
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    const u32 j = (tid >> 7) + 4 * k;
+                    if (lane == 0 && j < m) t5_red_add64(cin + (size_t)j * 2 + h, v);
+                }
+        }
+    }
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tm) : "memory");
 }
 
 // Returns 0 when launched; -1 when this shape is not served here (the caller falls back to the mma.sync kernel).
-int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
-                              u32 k0, u32 kcount, cudaStream_t st) {
+template <bool PROT>
+static int launch_t5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 k0, u32 kcount,
+                     cudaStream_t st, u64* cin, u64* cout, const BconvInjList& inj) {
     static const bool off = getenv("B200FHE_BCONV_NO_TC5") != nullptr;
     if (off || !btab5 || m > 16 || N % kT5Rows || N < 4096) return -1;
     static int sms = 0;
@@ -195,16 +258,31 @@ int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaFuncSetAttribute(k_bconv_contract_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(T5Smem) + 1024) != cudaSuccess) return -1;
+        if (cudaFuncSetAttribute(k_bconv_contract_tc5<PROT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(T5Smem) + 1024) != cudaSuccess)
+            return -1;
         attr = true;
     }
     const u32 n_tiles = N / kT5Rows;
     for (u32 off_k = 0; off_k < kcount; off_k += kT5MaxChunks * kT5Chunk) {
         const u32 kc = kcount - off_k < (u32)(kT5MaxChunks * kT5Chunk) ? kcount - off_k : (u32)(kT5MaxChunks * kT5Chunk);
         const u32 grid = n_tiles < (u32)sms ? n_tiles : (u32)sms;
-        k_bconv_contract_tc5<<<grid, kT5Threads, sizeof(T5Smem) + 1024, st>>>(y, out + (size_t)off_k * N, mods, dst_idx, btab5, N, m, k0 + off_k, kc);
+        k_bconv_contract_tc5<PROT><<<grid, kT5Threads, sizeof(T5Smem) + 1024, st>>>(y, out + (size_t)off_k * N, mods, dst_idx, btab5, N, m, k0 + off_k,
+                                                                                      kc, off_k ? nullptr : cin, cout, inj);
     }
     return 0;
+}
+
+int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
+                              u32 k0, u32 kcount, cudaStream_t st) {
+    BconvInjList none;
+    none.n = 0;
+    return launch_t5<false>(y, out, mods, dst_idx, btab5, N, m, k0, kcount, st, nullptr, nullptr, none);
+}
+
+int launch_bconv_contract_tc5_prot(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
+                                   u32 k0, u32 kcount, cudaStream_t st, u64* cin, u64* cout, const BconvInjList& inj) {
+    if (!cout) return -1;
+    return launch_t5<true>(y, out, mods, dst_idx, btab5, N, m, k0, kcount, st, cin, cout, inj);
 }
 
 }  // namespace b200

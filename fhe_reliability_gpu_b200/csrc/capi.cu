@@ -941,7 +941,7 @@ int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uin
     unsigned long long nl2_ = 0;
     int rc = launch_bconv_modup_protected((const u64*)d_in, (u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_src, p->d_dst, p->d_inv, p->d_hat, p->d_btab,
                                           (u32)p->ctx->N, (u32)p->m, (u32)p->K, cur, nxt, d_verdict, (u64*)d_sums, inject, (u32)n_inject,
-                                          (cudaStream_t)stream, &nl2_, (u64*)d_out_hi, (u32)k_split);
+                                          (cudaStream_t)stream, &nl2_, (u64*)d_out_hi, (u32)k_split, p->d_btab5);
     g_launches += nl2_;
     if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "bconv_modup_protected: unsupported plan");
     CK(cudaGetLastError());

@@ -66,11 +66,23 @@ int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const 
 // tcgen05 / TMEM contraction (bconv_tc5.cu); returns -1 when the shape is not served there (caller falls back to launch_bconv_contract_tc)
 int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
                               u32 k0, u32 kcount, cudaStream_t s);
+struct BconvInj {          // device copy of b200fhe_bconv_inject
+    u32 stage, limb;
+    u64 coeff, mask;
+};
+constexpr int kBconvMaxInj = 8;
+struct BconvInjList {
+    BconvInj e[kBconvMaxInj];
+    u32 n;
+};
+// checksum-carrying flavour of the tcgen05 contraction: cin [m][2] / cout [K][2] sums of the 32-bit halves of the words read / stored
+int launch_bconv_contract_tc5_prot(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
+                                   u32 k0, u32 kcount, cudaStream_t s, u64* cin, u64* cout, const BconvInjList& inj);
 // checksum-carrying ModUp of one digit (scale + tensor-core contraction + finalize); counters: 6 m + 2 K words of scratch
 int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* mods, const u32* src_idx, const u32* dst_idx,
                                  const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
                                  u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches,
-                                 u64* out_hi = nullptr, u32 k_split = 0);
+                                 u64* out_hi = nullptr, u32 k_split = 0, const uint4* btab5 = nullptr);
 
 }  // namespace b200
 
