@@ -43,6 +43,7 @@ SIGNATURES = {
     "b200fhe_four_step_protected_host": (i32, [u64, u64, sz, U64P, U64P, sz, U64P, C.POINTER(C.c_uint32), vp, sz, i32]),
     "b200fhe_relia_op_ranges": (i32, [sz, U64P, U64P, U64P]),
     "b200fhe_relia_four_step_host": (i32, [u64, u64, sz, i32, U64P, U64P, U64P, sz, vp, sz, C.POINTER(C.c_uint32), i32]),
+    "b200fhe_relia_standard_host": (i32, [u64, u64, sz, U64P, U64P, U64P, sz, vp, sz, C.POINTER(C.c_uint32), i32]),
     "b200fhe_pmult_accum": (i32, [vp, C.POINTER(vp), C.POINTER(vp), sz, vp, sz, sz, sz, i32, vp]),
     "b200fhe_pmult_accum_host": (i32, [vp, U64P, U64P, sz, U64P, sz, sz, sz]),
     "b200fhe_bconv_create": (i32, [vp, C.POINTER(i32), i32, C.POINTER(i32), i32, C.POINTER(vp)]),
@@ -486,6 +487,35 @@ def relia_four_step_host(q, g, a, weights, faults=(), fold_bits=4, want_out=True
     flags = np.zeros(trials, dtype=np.uint32)
     check(lib().b200fhe_relia_four_step_host(q, g, N, fold_bits, _p(a), _p(out) if want_out else None, _p(weights), trials,
                                              C.cast(arr, vp), nf, flags.ctypes.data_as(C.POINTER(C.c_uint32)), device))
+    return out, flags
+
+
+def _relia_faults(faults):
+    if isinstance(faults, np.ndarray):          # structured array with b200fhe_relia_fault's layout (24-byte records)
+        assert faults.dtype.itemsize == C.sizeof(ReliaFault) and faults.flags.c_contiguous
+        return faults.ctypes.data_as(vp), len(faults)
+    if isinstance(faults, C.Array):
+        return faults, len(faults)
+    faults = list(faults)
+    arr = (ReliaFault * max(len(faults), 1))()
+    for i, (tr, op, kind, payload) in enumerate(faults):
+        arr[i] = ReliaFault(int(tr), int(kind), int(op), int(payload))
+    return arr, len(faults)
+
+
+def relia_standard_host(q, g, a, weights, faults=(), want_out=True, device=0):
+    """One trial per row of non_four_step_ntt_sim.cpp (standard NTT + lazy bucket check + global check): a [trials][N],
+    weights [trials][N]; faults as relia_four_step_host, ops in [0, (N/2) log2 N).  Returns (out or None, flags): bit 0 lazy,
+    bit 1 global."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    weights = np.ascontiguousarray(weights, dtype=np.uint64)
+    trials, N = a.shape
+    assert weights.shape == a.shape
+    arr, nf = _relia_faults(faults)
+    out = np.zeros_like(a) if want_out else None
+    flags = np.zeros(trials, dtype=np.uint32)
+    check(lib().b200fhe_relia_standard_host(q, g, N, _p(a), _p(out) if want_out else None, _p(weights), trials, C.cast(arr, vp), nf,
+                                            flags.ctypes.data_as(C.POINTER(C.c_uint32)), device))
     return out, flags
 
 

@@ -160,6 +160,94 @@ __global__ void __launch_bounds__(256) k_relia_four_step(const u64* __restrict__
     if (threadIdx.x == 0) flags[tr] = flag;
 }
 
+// ---- the baseline the reference compared against: standard iterative NTT + lazy bucket check + global check
+// (rfhe_framewk/src/ntt_test/non_four_step_ntt_sim.cpp) ---------------------------------------------------------------
+// ntt_standard_lazy (:164-218): one length-N radix-2 DIT transform whose every product v = A[k+half] * w is handed to the
+// LazyChecker (:135-158) twice -- the value the butterfly consumes (after injection) into sum_out[op % buckets], the
+// UNREDUCED 128-bit product into sum_ref[op % buckets] -- and the check is sum_out == sum_ref (mod Q) per bucket: a
+// reduction-unit fault shows up in its bucket.  Device form: the sums are exact integers kept as sums of 32-bit pieces (two of
+// v, four of the product; each < 2^32 * N/2 log N / buckets), reduced mod Q once at the end.  Operation numbering as in
+// sub_ntts (stage-major, then group, then k: the simulator's loop order).
+// lz: [buckets][6] accumulators, pieces 0-1 of v, 2-5 of the product.
+__device__ void std_ntt_lazy(u64* x, u64* tmp, int lg, const u64* pw, const ReliaFault* f, u32 nf, const B200Mod& m, u64* lz, u32 buckets) {
+    const u32 len = 1u << lg;
+    for (u32 i = threadIdx.x; i < len; i += blockDim.x) tmp[brev(i, lg)] = x[i];
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < len; i += blockDim.x) x[i] = tmp[i];
+    __syncthreads();
+    const u32 hb = len >> 1;
+    for (int s = 0; s < lg; s++) {
+        const u32 half = 1u << s;
+        for (u32 b = threadIdx.x; b < hb; b += blockDim.x) {
+            const u32 grp = b >> s, k = b & (half - 1);
+            u64* p = x + (grp << (s + 1)) + k;
+            const u64 w = pw[(size_t)k << (lg - 1 - s)];
+            const u64 u = p[0], t = p[half];
+            u64 v = mm(t, w, m);
+            const long long op = (long long)s * hb + b;
+            if (nf) v = corrupt(v, op, f, nf, m);
+            if (lz) {
+                const u64 lo = t * w, hi = __umul64hi(t, w);
+                u64* a = lz + (size_t)(op % buckets) * 6;
+                atomicAdd((unsigned long long*)a + 0, (unsigned long long)(v & 0xffffffffull));
+                atomicAdd((unsigned long long*)a + 1, (unsigned long long)(v >> 32));
+                atomicAdd((unsigned long long*)a + 2, (unsigned long long)(lo & 0xffffffffull));
+                atomicAdd((unsigned long long*)a + 3, (unsigned long long)(lo >> 32));
+                atomicAdd((unsigned long long*)a + 4, (unsigned long long)(hi & 0xffffffffull));
+                atomicAdd((unsigned long long*)a + 5, (unsigned long long)(hi >> 32));
+            }
+            p[0] = addm(u, v, m.q);
+            p[half] = addm(u, m.q - v, m.q);
+        }
+        __syncthreads();
+    }
+}
+
+// sm: pw[N] | a[N] input | b[N] transform | c[N] scratch | wv[N] | wh[N] | lz[buckets][6] | red[32]
+__global__ void __launch_bounds__(256) k_relia_standard(const u64* __restrict__ in, u64* __restrict__ out, const u64* __restrict__ wts, u32 N, int lg,
+                                                        B200Mod m, const u64* __restrict__ pw_g, u32 buckets, const ReliaFault* faults,
+                                                        const u32* fault_begin, u32* flags) {
+    extern __shared__ u64 sm[];
+    u64 *pw = sm, *a = sm + N, *b = a + N, *c = b + N, *wv = c + N, *wh = wv + N, *lz = wh + N, *red = lz + (size_t)buckets * 6;
+    const u32 tr = blockIdx.x;
+    const u64 q = m.q;
+    const ReliaFault* f = faults + fault_begin[tr];
+    const u32 nf = fault_begin[tr + 1] - fault_begin[tr];
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) {
+        pw[i] = pw_g[i];
+        const u64 v = in[(size_t)tr * N + i] % q;
+        a[i] = v; b[i] = v;
+        const u64 w = wts[(size_t)tr * N + i] % q;
+        wv[i] = w; wh[i] = w;
+    }
+    for (u32 i = threadIdx.x; i < buckets * 6; i += blockDim.x) lz[i] = 0;
+    __syncthreads();
+    std_ntt_lazy(b, c, lg, pw, f, nf, m, lz, buckets);
+    u32 flag = 0;
+    {   // LazyChecker::verify (:151-157)
+        u32 bad = 0;
+        const u64 r32 = ((u64)1 << 32) % q, r64 = mm(r32, r32, m), r96 = mm(r64, r32, m);
+        for (u32 i = threadIdx.x; i < buckets; i += blockDim.x) {
+            const u64* e = lz + (size_t)i * 6;
+            const u64 so = addm(e[0] % q, mm(e[1] % q, r32, m), q);
+            u64 sr = addm(e[2] % q, mm(e[3] % q, r32, m), q);
+            sr = addm(sr, mm(e[4] % q, r64, m), q);
+            sr = addm(sr, mm(e[5] % q, r96, m), q);
+            if (so != sr) bad = 1;
+        }
+        if (__syncthreads_or(bad)) flag |= 1;
+    }
+    // check_abft_global (:220-235): NTT(w) . input == w . output
+    std_ntt_lazy(wh, c, lg, pw, nullptr, 0, m, nullptr, 1);
+    u64 l = 0, r = 0;
+    for (u32 i = threadIdx.x; i < N; i += blockDim.x) { l = addm(l, mm(wh[i], a[i], m), q); r = addm(r, mm(wv[i], b[i], m), q); }
+    l = block_sum(l, q, red); r = block_sum(r, q, red);
+    if (l != r) flag |= 2;
+    if (out)
+        for (u32 i = threadIdx.x; i < N; i += blockDim.x) out[(size_t)tr * N + i] = b[i];
+    if (threadIdx.x == 0) flags[tr] = flag;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -245,5 +333,71 @@ extern "C" int b200fhe_relia_four_step_host(uint64_t q, uint64_t g, size_t N, in
     if (e == cudaSuccess) e = cudaMemcpy(h_flags, d_flags, trials * 4, cudaMemcpyDeviceToHost);
     cudaFree(d_in); cudaFree(d_out); cudaFree(d_w); cudaFree(d_pw); cudaFree(d_begin); cudaFree(d_flags); cudaFree(d_f);
     if (e != cudaSuccess) return b200_set_err(B200FHE_ECUDA, "relia: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+extern "C" int b200fhe_relia_standard_host(uint64_t q, uint64_t g, size_t N, const uint64_t* h_in, uint64_t* h_out, const uint64_t* h_weights,
+                                           size_t trials, const b200fhe_relia_fault* faults, size_t n_faults, uint32_t* h_flags, int device) {
+    if (!h_in || !h_weights || !h_flags || (n_faults && !faults)) return b200_set_err(B200FHE_EINVAL, "relia_standard: null argument");
+    int lg = 0;
+    while (((size_t)1 << lg) < N) lg++;
+    if (((size_t)1 << lg) != N || N < 2 || N > 4096) return b200_set_err(B200FHE_EUNSUPPORTED, "relia_standard: N=%zu must be a power of two in [2, 4096]", N);
+    if (q < 3 || (q >> 60) || !nt::is_prime(q) || (q - 1) % N)
+        return b200_set_err(B200FHE_EINVAL, "relia_standard: modulus must be a prime < 2^60 with N | q-1");
+    if (trials == 0) return 0;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return b200_set_err(B200FHE_ECUDA, "no CUDA device: this library has no CPU fallback");
+    if (device < 0 || device >= ndev) return b200_set_err(B200FHE_EINVAL, "device %d of %d", device, ndev);
+    cudaSetDevice(device);
+    const uint64_t wN = nt::powmod(g, (q - 1) / N, q);
+    if (nt::powmod(wN, N / 2, q) != q - 1) return b200_set_err(B200FHE_EINVAL, "relia_standard: g=%llu does not give a primitive N-th root", (unsigned long long)g);
+    std::vector<uint64_t> pw(N);
+    pw[0] = 1;
+    for (size_t i = 1; i < N; i++) pw[i] = nt::mulmod(pw[i - 1], wN, q);
+    const uint64_t total = (uint64_t)(N / 2) * lg;                 // the simulator's dry-run op count (:262-265)
+    uint32_t buckets = 1;
+    while ((uint64_t)(buckets + 1) * (buckets + 1) <= N) buckets++;   // (int)sqrt(n) (:170)
+    std::vector<uint32_t> begin(trials + 1, 0);
+    for (size_t i = 0; i < n_faults; i++) {
+        if (faults[i].trial >= trials || faults[i].op >= total || faults[i].kind < 1 || faults[i].kind > 2)
+            return b200_set_err(B200FHE_EINVAL, "relia_standard: fault %zu out of range", i);
+        begin[faults[i].trial + 1]++;
+    }
+    for (size_t t = 0; t < trials; t++) begin[t + 1] += begin[t];
+    std::vector<ReliaFault> fl(n_faults ? n_faults : 1);
+    {
+        std::vector<uint32_t> pos(begin.begin(), begin.end() - 1);
+        for (size_t i = 0; i < n_faults; i++) fl[pos[faults[i].trial]++] = ReliaFault{faults[i].op, faults[i].payload, faults[i].kind, 0};
+    }
+    const B200Mod m = b200_make_mod(q, 0, 1);
+    u64 *d_in = nullptr, *d_out = nullptr, *d_w = nullptr, *d_pw = nullptr;
+    u32 *d_begin = nullptr, *d_flags = nullptr;
+    ReliaFault* d_f = nullptr;
+    cudaError_t e = cudaMalloc(&d_in, trials * N * 8);
+    if (e == cudaSuccess && h_out) e = cudaMalloc(&d_out, trials * N * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_w, trials * N * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_pw, N * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_begin, (trials + 1) * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_flags, trials * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_f, sizeof(ReliaFault) * fl.size());
+    if (e == cudaSuccess) e = cudaMemcpy(d_in, h_in, trials * N * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_w, h_weights, trials * N * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_pw, pw.data(), N * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_begin, begin.data(), (trials + 1) * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_f, fl.data(), sizeof(ReliaFault) * fl.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        const size_t smem = (6 * N + (size_t)buckets * 6 + 32) * 8;
+        static bool attr_set = false;
+        if (!attr_set) { e = cudaFuncSetAttribute(k_relia_standard, cudaFuncAttributeMaxDynamicSharedMemorySize, (6 * 4096 + 64 * 6 + 32) * 8); attr_set = e == cudaSuccess; }
+        if (e == cudaSuccess) {
+            k_relia_standard<<<(unsigned)trials, 256, smem>>>(d_in, d_out, d_w, (u32)N, lg, m, d_pw, buckets, d_f, d_begin, d_flags);
+            b200_count_launches(1);
+            e = cudaGetLastError();
+        }
+    }
+    if (e == cudaSuccess && h_out) e = cudaMemcpy(h_out, d_out, trials * N * 8, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(h_flags, d_flags, trials * 4, cudaMemcpyDeviceToHost);
+    cudaFree(d_in); cudaFree(d_out); cudaFree(d_w); cudaFree(d_pw); cudaFree(d_begin); cudaFree(d_flags); cudaFree(d_f);
+    if (e != cudaSuccess) return b200_set_err(B200FHE_ECUDA, "relia_standard: %s", cudaGetErrorString(e));
     return 0;
 }

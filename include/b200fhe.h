@@ -217,6 +217,16 @@ int b200fhe_relia_four_step_host(uint64_t q, uint64_t g, size_t N, int fold_bits
                                  const uint64_t* h_weights, size_t trials, const b200fhe_relia_fault* faults, size_t n_faults,
                                  uint32_t* h_flags, int device);
 
+/* The baseline the reference compared its scheme against (rfhe_framewk/src/ntt_test/non_four_step_ntt_sim.cpp): a standard
+ * iterative cyclic NTT (ntt_standard_lazy :164-218) with the lazy-reduction bucket checker (LazyChecker :135-158: per
+ * operation, the stored product and the UNREDUCED product go into bucket op % (int)sqrt(N); the sums must agree mod q) and
+ * the global check with random weights (check_abft_global :220-235).  One CTA per trial.  h_in [trials][N]; h_out
+ * [trials][N] (optional) the transform (natural order in and out); h_weights [trials][N] the global check's w; faults address
+ * the (N/2) log2 N products in loop order (stage-major), same kinds as above.  h_flags[t]: bit 0 = the lazy check failed,
+ * bit 1 = the global check failed; the simulator's `detected` (:311) is h_flags[t] != 0.  N a power of two <= 4096. */
+int b200fhe_relia_standard_host(uint64_t q, uint64_t g, size_t N, const uint64_t* h_in, uint64_t* h_out, const uint64_t* h_weights,
+                                size_t trials, const b200fhe_relia_fault* faults, size_t n_faults, uint32_t* h_flags, int device);
+
 /* ---- ct x pt multiply-accumulate (config C3) ------------------------------- */
 
 /* out[p][l][i] = sum_{k<n_terms} ct_k[p][l][i] * pt_k[l][i] mod q_{start_mod+l}, NTT domain.

@@ -75,6 +75,7 @@ def lib():
             ("orc_ntt_forward_polys", None, [U64P, i32, i32, i32, U64P, U64P, U64P]),
             ("orc_ntt_inverse_polys", None, [U64P, i32, i32, i32, U64P, U64P, U64P]),
             ("orc_relia_four_step", i32, [u64, u64, i32, i32, U64P, U64P, U64P, C.c_void_p, i32]),
+            ("orc_relia_standard", i32, [u64, u64, i32, U64P, U64P, U64P, C.c_void_p, i32]),
             ("orc_set_threads", None, [i32]),
             ("orc_get_threads", i32, []),
             ("orc_abft_weights", None, [i32, U64P]),
@@ -432,6 +433,20 @@ def relia_four_step(q, g, a, weights, faults=(), fold_bits=4):
         arr[i] = OrcReliaFault(int(op), int(kind), 0, int(payload))
     out = np.zeros_like(a)
     flags = lib().orc_relia_four_step(q, g, a.size, fold_bits, _p(a), _p(out), _p(weights), C.cast(arr, C.c_void_p), len(faults))
+    return out, int(flags)
+
+
+def relia_standard(q, g, a, weights, faults=()):
+    """One trial of non_four_step_ntt_sim.cpp: a [N], weights [N] (the global check's random w), faults (op, kind, payload).
+    Returns (out [N], flags): bit 0 the lazy bucket check failed, bit 1 the global check failed."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    weights = np.ascontiguousarray(weights, dtype=np.uint64)
+    faults = list(faults)
+    arr = (OrcReliaFault * max(len(faults), 1))()
+    for i, (op, kind, payload) in enumerate(faults):
+        arr[i] = OrcReliaFault(int(op), int(kind), 0, int(payload))
+    out = np.zeros_like(a)
+    flags = lib().orc_relia_standard(q, g, a.size, _p(a), _p(out), _p(weights), C.cast(arr, C.c_void_p), len(faults))
     return out, int(flags)
 
 

@@ -73,3 +73,19 @@ def within_3_sigma(k1, n1, k2, n2):
     p = (k1 + k2) / (n1 + n2)
     sd = (p * (1 - p) * (1.0 / n1 + 1.0 / n2)) ** 0.5
     return abs(k1 / n1 - k2 / n2) <= 3.0 * sd + 1.0 / min(n1, n2)
+
+
+STD_SIM = os.path.join(ROOT, "oracle", "_ref", "non_four_step_ntt_sim")
+
+
+def run_standard_simulator(N, q_bits, trials):
+    """{scenario: dict(det=count, lazy=.., inter=.., trials=..)} from the table non_four_step_ntt_sim prints (:267-330)."""
+    txt = subprocess.run([STD_SIM, "--N", str(N), "--q-bits", str(q_bits), "--trials", str(trials)],
+                         capture_output=True, text=True, timeout=1800, check=True).stdout
+    q = int(re.search(r"Q=(\d+)", txt).group(1))
+    table = {}
+    for line in txt.splitlines():
+        m = re.match(r"\s*(\S+)\s+Standard NTT\s+([\d.]+)\s+([\d.]+)\s+\|\s+(\d+)\s+(\d+)", line)
+        if m:
+            table[m.group(1)] = dict(det=round(float(m.group(2)) * trials), lazy=int(m.group(4)), inter=int(m.group(5)), trials=trials)
+    return q, table
