@@ -257,8 +257,13 @@ def main():
         pkg.binding.check(lib.b200fhe_nwt_forward(ctx._h, dp, npoly, L, 0, sp))
     def fwd_prot():
         pkg.binding.check(lib.b200fhe_nwt_forward_protected(ctx._h, dp, npoly, L, 0, vp_, None, None, 0, sp))
+    def inv_plain():
+        pkg.binding.check(lib.b200fhe_nwt_backward(ctx._h, dp, npoly, L, 0, sp))
+    def inv_prot():
+        pkg.binding.check(lib.b200fhe_nwt_backward_protected(ctx._h, dp, npoly, L, 0, vp_, None, sp))
     abft_ms = {}
-    for name, fn in (("forward", fwd_plain), ("forward_protected", fwd_prot)):
+    flagged_inv = 0
+    for name, fn in (("inverse", inv_plain), ("inverse_protected", inv_prot), ("forward", fwd_plain), ("forward_protected", fwd_prot)):
         for _ in range(3):
             fn()
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -268,9 +273,13 @@ def main():
         a1.record(stream)
         torch.cuda.synchronize()
         abft_ms[name] = a0.elapsed_time(a1) / max(args.steps, 5)
+        if name == "inverse_protected":
+            flagged_inv = int(verdict.sum().item())
     abft = {"forward_ms": abft_ms["forward"], "forward_protected_ms": abft_ms["forward_protected"],
             "overhead_pct": 100.0 * (abft_ms["forward_protected"] / abft_ms["forward"] - 1.0),
             "faults_flagged_clean_run": int(verdict.sum().item()),
+            "inverse": {"ms": abft_ms["inverse"], "protected_ms": abft_ms["inverse_protected"],
+                        "overhead_pct": 100.0 * (abft_ms["inverse_protected"] / abft_ms["inverse"] - 1.0), "faults_flagged_clean_run": flagged_inv},
             "note": "t(protected)/t(unprotected)-1 on the same %d-limb batch; checksum fused into first load / last store" % (npoly * L)}
     peak, peak_src = peaks()
     dom = max(kern, key=kern.get)
@@ -322,6 +331,7 @@ def main():
         sub["modup"], sub["keyswitch"] = bench_sub.keyswitch_records(pkg, torch, O, peak, local, check=not NOCHECK)
         torch.cuda.empty_cache()
         sub["fold_check"] = bench_sub.fold_record(pkg, torch, O, peak, local, check=not NOCHECK)
+        sub["bgv"] = bench_sub.bgv_record(pkg, torch, peak, local)
         if world > 1:
             torch.cuda.empty_cache()
             sub["modup_sharded"] = bench_sub.modup_sharded_record(pkg, torch, dist, rank, world, local, peak)

@@ -112,6 +112,18 @@ def keyswitch_records(pkg, torch, O, peak, device, steps=10, check=True):
     g_up, g_ks = _graphed(torch, f_up), _graphed(torch, f_ks)
     ms_up = _timed(torch, g_up or f_up, steps)
     ms_ks = _timed(torch, g_ks or f_ks, steps)
+    # the checked flavours (eager): conversions only (f2 inside f1), then every limb-transform as well
+    ms_eager = _timed(torch, f_ks, steps)
+    verdict = torch.zeros((dnum + 2, total), dtype=torch.int32, device="cuda")
+    vntt = torch.zeros(ks.ntt_count(), dtype=torch.int32, device="cuda")
+    f_prot = lambda: ks.apply_protected(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr(), verdict.data_ptr(), stream=sp())
+    f_full = lambda: ks.apply_protected_full(d_c.data_ptr(), d_eq.data_ptr(), d_ep.data_ptr(), d_out.data_ptr(), verdict.data_ptr(), vntt.data_ptr(), stream=sp())
+    ref_out = d_out.clone()
+    ms_prot = _timed(torch, f_prot, steps)
+    same_prot = bool(torch.equal(ref_out, d_out))
+    ms_full = _timed(torch, f_full, steps)
+    same_full = bool(torch.equal(ref_out, d_out))
+    flagged = int(verdict.abs().sum().item()) + int(vntt.abs().sum().item())
     t_up = n_q + dnum * (total - alpha)
     mm_up = dnum * alpha * (1 + total - alpha) * N
     t_ks = t_up + 2 * n_p + 2 * n_q
@@ -130,7 +142,15 @@ def keyswitch_records(pkg, torch, O, peak, device, steps=10, check=True):
               "work_per_call": {"limb_transforms": t_ks, "bconv_mulmods": mm_ks},
               "roofline": {"bound": "hbm", "achieved": b_ks / (ms_ks * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": b_ks / (ms_ks * 1e-3) / 1e9 / peak,
                            "algorithmic_bytes_per_call": b_ks},
-              "parity_vs_oracle": par_ks, "parity_scope": "both output polynomials, all 48 limbs, bit-exact against the oracle composition"}
+              "parity_vs_oracle": par_ks, "parity_scope": "both output polynomials, all 48 limbs, bit-exact against the oracle composition",
+              "protected": {"ms_eager_unprotected": ms_eager,
+                            "conversions_checked": {"ms_eager": ms_prot, "overhead_pct": 100.0 * (ms_prot / ms_eager - 1.0), "checks": int(verdict.numel()),
+                                                    "same_output_bits": same_prot},
+                            "everything_checked": {"ms_eager": ms_full, "overhead_pct": 100.0 * (ms_full / ms_eager - 1.0),
+                                                   "checks": int(verdict.numel() + vntt.numel()), "same_output_bits": same_full},
+                            "faults_flagged_clean_run": flagged,
+                            "note": "b200fhe_keyswitch_apply_protected / _apply_protected_full: checksum-carrying conversions (tcgen05 contraction with "
+                                    "the sums fused), then a fused-checksum verdict per limb-transform as well; the evk inner product is not checked"}}
     ks.close()
     return rec_up, rec_ks
 
@@ -250,3 +270,48 @@ def modup_sharded_record(pkg, torch, dist, rank, world, local, peak, log_n=17, n
            "parity_vs_unsharded": parity, "parity_scope": "every owned limb of every digit on every rank, bit-exact against b200fhe_keyswitch_modup"}
     plan.close(); shard.close()
     return rec
+
+
+def bgv_record(pkg, torch, peak, device, steps=10):
+    """f3: the homomorphic steps of dotprod_test.cu:113-152 at its own parameters (N=16384, six 50-bit primes of which two special,
+    20-bit batching plain modulus): multiply, relinearize, mod-switch, rotate, timed per call on device-resident ciphertexts; the
+    pipeline's result is decrypted and compared with the slot-wise product (the reference's own correctness criterion)."""
+    log_n, N = 14, 1 << 14
+    tq = pkg.primes_create(N, [50] * 6)
+    tt = pkg.primes_create(N, [20])[0]
+    bgv = pkg.binding.Bgv(log_n, tq, 2, tt, seed=7, device=device)
+    rng = np.random.default_rng(3)
+    xa, xb = rng.integers(0, 100, N).astype(np.uint64), rng.integers(0, 100, N).astype(np.uint64)
+    ca = torch.zeros((2, 4, N), dtype=torch.int64, device="cuda"); cb = torch.zeros_like(ca)
+    bgv.encrypt(bgv.encode(xa), ca.data_ptr()); bgv.encrypt(bgv.encode(xb), cb.data_ptr())
+    c3 = torch.zeros((3, 4, N), dtype=torch.int64, device="cuda")
+    lo = torch.zeros((2, 3, N), dtype=torch.int64, device="cuda")
+    lib = pkg.lib()
+    l0 = lib.b200fhe_launch_count()
+    bgv.multiply(ca.data_ptr(), cb.data_ptr(), c3.data_ptr(), 4)
+    bgv.relinearize(c3.data_ptr(), 4)
+    cf = bgv.mod_switch_to_next(c3[:2].contiguous().data_ptr(), 2, 4, lo.data_ptr())
+    bgv.rotate(lo.data_ptr(), 3, 1)
+    torch.cuda.synchronize()
+    l1 = lib.b200fhe_launch_count()
+    prod = xa * xb % np.uint64(tt)
+    want = np.concatenate([np.roll(prod[:N // 2], -1), np.roll(prod[N // 2:], -1)])
+    ok = bool((bgv.decode(bgv.decrypt(lo.data_ptr(), 2, 3, cf)) == want).all())
+    two = c3[:2].contiguous()
+    scratch = torch.zeros_like(c3)
+    def relin():
+        scratch.copy_(c3_fresh)
+        bgv.relinearize(scratch.data_ptr(), 4)
+    bgv.multiply(ca.data_ptr(), cb.data_ptr(), c3.data_ptr(), 4)
+    c3_fresh = c3.clone()
+    ms = {"multiply": _timed(torch, lambda: bgv.multiply(ca.data_ptr(), cb.data_ptr(), c3.data_ptr(), 4), steps),
+          "copy_3x4_limbs": _timed(torch, lambda: scratch.copy_(c3_fresh), steps),
+          "copy_plus_relinearize": _timed(torch, relin, steps),
+          "mod_switch_to_next": _timed(torch, lambda: bgv.mod_switch_to_next(two.data_ptr(), 2, 4, lo.data_ptr()), steps),
+          "rotate_rows_1": _timed(torch, lambda: bgv.rotate(lo.data_ptr(), 3, 1), steps)}
+    bgv.close()
+    return {"workload": "f3: BGV steps of dotprod_test.cu (N=16384, {50 x 6} with 2 special primes, t = 20-bit batching prime), device-resident",
+            "ms": ms, "launches_multiply_relin_modswitch_rotate": int(l1 - l0), "decrypts_to_slotwise_product_rotated": ok,
+            "note": "per call through b200fhe_bgv_* (what shim/phantom_bgv.h forwards to); relinearize works in place, so it is timed with the "
+                    "copy that restores its input (the copy alone is listed)"}
+
