@@ -137,7 +137,7 @@ extern "C" int b200fhe_four_step_protected_host(uint64_t mod, uint64_t g, size_t
     while (n * n < N) n++;
     if (n * n != N || N < 4 || N > 4096) return b200_set_err(B200FHE_EUNSUPPORTED, "four_step: N=%zu must be a perfect square in [4, 4096]", N);
     if (mod < 3 || (mod >> 60) || !nt::is_prime(mod) || (mod - 1) % N) return b200_set_err(B200FHE_EINVAL, "four_step: modulus must be a prime < 2^60 with N | mod-1");
-    if (n_plan > B200FHE_MAX_INJECT) return b200_set_err(B200FHE_EINVAL, "four_step: too many injections");
+    if (n_plan > (size_t)B200FHE_MAX_INJECT * (batch ? batch : 1)) return b200_set_err(B200FHE_EINVAL, "four_step: too many injections (at most %d per transform of the batch)", B200FHE_MAX_INJECT);
     if (batch == 0) return 0;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return b200_set_err(B200FHE_ECUDA, "no CUDA device: this library has no CPU fallback");

@@ -185,7 +185,8 @@ typedef struct b200fhe_fs_inject {
  * factorisation Pi_k (I x W_n) S D (I x W_n) Pi_t with its protection equality
  * sum(C) == colsum(A) . rowsum(B) (:185-194) evaluated on both matrix stages in the same kernel.
  * h_checks[t] = {lhs1, rhs1, lhs2, rhs2}; h_verdict[t] bit 0 / bit 1 = stage 1 / stage 2 check failed.
- * Host buffers in and out (the prototype's lists). */
+ * Host buffers in and out (the prototype's lists).  n_plan <= B200FHE_MAX_INJECT * batch; several entries may hit one
+ * transform (a line fault, MCF-CLE of four_step_ntt_protected.cpp:212-222, is n entries) but not one row twice. */
 int b200fhe_four_step_protected_host(uint64_t mod, uint64_t g, size_t N, const uint64_t* h_in, uint64_t* h_out, size_t batch,
                                      uint64_t* h_checks, uint32_t* h_verdict, const b200fhe_fs_inject* plan, size_t n_plan,
                                      int device);
