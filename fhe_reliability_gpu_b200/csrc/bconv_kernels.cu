@@ -401,7 +401,7 @@ static void launch_tc(const u64* y, u64* out, const B200Mod* mods, const u32* ds
     const u32 rounds = (blocks + gx - 1) / gx;
     gx = (blocks + rounds - 1) / rounds;
     const size_t smem = per_target * (per_cta < kcount ? per_cta : kcount) + fixed;
-    cudaFuncSetAttribute(k_bconv_contract_tc<KS, PROT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget + 4096);
+    (void)set_smem_once<k_bconv_contract_tc<KS, PROT>>(budget + 4096);     // on failure the launch below fails and the caller's cudaGetLastError reports it
     k_bconv_contract_tc<KS, PROT><<<dim3(gx, ny), kTcWarps * 32, smem, s>>>(y, out, mods, dst_idx, btab, N, m, K, k0, kcount, per_cta,
                                                                               cin, cout, inj);
 }
@@ -581,7 +581,7 @@ int launch_bconv_contract(const u64* y, u64* out, const B200Mod* mods, const u32
     if (!kcount) return 0;
     const size_t smem = sizeof(u64) * ((size_t)m * 256 + (size_t)kBcT * m);
     if (smem > 200 * 1024) return -1;
-    cudaFuncSetAttribute(k_bconv_contract, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (set_smem_once<k_bconv_contract>(200 * 1024) != cudaSuccess) return -1;
     // y is staged once per CTA; split the output tiles over grid.y only when there are too few CTAs to fill 148 SMs
     const u32 nx = (N + 255) / 256, n_tiles = (kcount + kBcT - 1) / kBcT;
     u32 ny = nx >= 592 ? 1 : (592 + nx - 1) / nx;

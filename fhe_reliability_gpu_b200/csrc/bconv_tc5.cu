@@ -252,16 +252,12 @@ static int launch_t5(const u64* y, u64* out, const B200Mod* mods, const u32* dst
                      cudaStream_t st, u64* cin, u64* cout, const BconvInjList& inj) {
     static const bool off = getenv("B200FHE_BCONV_NO_TC5") != nullptr;
     if (off || !btab5 || m > 16 || N % kT5Rows || N < 4096) return -1;
-    static int sms = 0;
-    static bool attr = false;
-    if (!attr) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaFuncSetAttribute(k_bconv_contract_tc5<PROT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(T5Smem) + 1024) != cudaSuccess)
-            return -1;
-        attr = true;
-    }
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    static int sm_count[64] = {};
+    if (!sm_count[dev & 63]) cudaDeviceGetAttribute(&sm_count[dev & 63], cudaDevAttrMultiProcessorCount, dev);
+    sms = sm_count[dev & 63];
+    if (sms <= 0 || set_smem_once<k_bconv_contract_tc5<PROT>>(sizeof(T5Smem) + 1024) != cudaSuccess) return -1;
     const u32 n_tiles = N / kT5Rows;
     for (u32 off_k = 0; off_k < kcount; off_k += kT5MaxChunks * kT5Chunk) {
         const u32 kc = kcount - off_k < (u32)(kT5MaxChunks * kT5Chunk) ? kcount - off_k : (u32)(kT5MaxChunks * kT5Chunk);

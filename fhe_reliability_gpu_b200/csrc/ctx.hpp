@@ -4,6 +4,7 @@
 // DNTTTable.init/set per limb): moduli, Barrett/Shoup constants and the
 // bit-reversed twiddle tables, resident on one device.
 #pragma once
+#include <atomic>
 #include <cstddef>
 #include <cstdint>
 #include <string>
@@ -83,6 +84,21 @@ int launch_bconv_modup_protected(const u64* x, u64* y, u64* out, const B200Mod* 
                                  const ulonglong2* inv, const u64* hat, const uint2* btab, u32 N, u32 m, u32 K, u64* counters,
                                  u64* next_counters, u32* verdict, u64* sums, const void* inj_host, u32 n_inj, cudaStream_t s, unsigned long long* launches,
                                  u64* out_hi = nullptr, u32 k_split = 0, const uint4* btab5 = nullptr);
+
+// Opt-in dynamic shared memory above 48 KiB, set once per kernel instantiation (the kernel is a non-type template argument: one
+// static per instantiation, not per function-pointer type) and per device (the attribute belongs to the device's context).
+template <auto Kernel>
+static inline cudaError_t set_smem_once(size_t smem) {
+    static std::atomic<unsigned long long> done{0};
+    if (smem <= 48 * 1024) return cudaSuccess;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_relaxed) & bit) return cudaSuccess;
+    const cudaError_t rc = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (rc == cudaSuccess) done.fetch_or(bit, std::memory_order_relaxed);
+    return rc;
+}
 
 }  // namespace b200
 

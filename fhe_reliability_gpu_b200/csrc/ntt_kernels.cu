@@ -511,18 +511,7 @@ __global__ void k_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 s
 // cudaFuncAttributeMaxDynamicSharedMemorySize is set once per kernel instantiation (not on every launch), and checked
 // (the kernel is a non-type template argument: one static per instantiation, not per function-pointer TYPE)
 // and per device: the attribute belongs to the device's context)
-template <auto Kernel>
-static cudaError_t set_smem_once(size_t smem) {
-    static std::atomic<unsigned long long> done{0};
-    if (smem <= 48 * 1024) return cudaSuccess;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    const unsigned long long bit = 1ull << (dev & 63);
-    if (done.load(std::memory_order_relaxed) & bit) return cudaSuccess;
-    const cudaError_t rc = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (rc == cudaSuccess) done.fetch_or(bit, std::memory_order_relaxed);
-    return rc;
-}
+// set_smem_once<Kernel>(smem): ctx.hpp
 // row passes: pairs of polynomials share a CTA (and its twiddle tile); an odd last polynomial runs the one-poly form
 // Measured on B200 (profiles/r2e_ablations.txt): the paired form is NOT faster (fwd 107 vs 99 us, inv 103 vs 98.5 us per 288-limb
 // batch) -- the row passes are bound by their own instruction stream, not by twiddle traffic or occupancy -- so it stays an

@@ -321,8 +321,7 @@ extern "C" int b200fhe_relia_four_step_host(uint64_t q, uint64_t g, size_t N, in
     if (e == cudaSuccess) e = cudaMemcpy(d_f, fl.data(), sizeof(ReliaFault) * fl.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         const size_t smem = (4 * N + 4 * nm + 32) * 8;
-        static bool attr_set = false;
-        if (!attr_set) { e = cudaFuncSetAttribute(k_relia_four_step, cudaFuncAttributeMaxDynamicSharedMemorySize, (4 * 4096 + 4 * 64 + 32) * 8); attr_set = e == cudaSuccess; }
+        e = set_smem_once<k_relia_four_step>((4 * 4096 + 4 * 64 + 32) * 8);
         if (e == cudaSuccess) {
             k_relia_four_step<<<(unsigned)trials, 256, smem>>>(d_in, d_out, d_w, (u32)N, lg1, lg2, m, d_pw, fold_bits, d_f, d_begin, d_flags);
             b200_count_launches(1);
@@ -387,8 +386,7 @@ extern "C" int b200fhe_relia_standard_host(uint64_t q, uint64_t g, size_t N, con
     if (e == cudaSuccess) e = cudaMemcpy(d_f, fl.data(), sizeof(ReliaFault) * fl.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         const size_t smem = (6 * N + (size_t)buckets * 6 + 32) * 8;
-        static bool attr_set = false;
-        if (!attr_set) { e = cudaFuncSetAttribute(k_relia_standard, cudaFuncAttributeMaxDynamicSharedMemorySize, (6 * 4096 + 64 * 6 + 32) * 8); attr_set = e == cudaSuccess; }
+        e = set_smem_once<k_relia_standard>((6 * 4096 + 64 * 6 + 32) * 8);
         if (e == cudaSuccess) {
             k_relia_standard<<<(unsigned)trials, 256, smem>>>(d_in, d_out, d_w, (u32)N, lg, m, d_pw, buckets, d_f, d_begin, d_flags);
             b200_count_launches(1);
