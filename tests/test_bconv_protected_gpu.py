@@ -30,6 +30,24 @@ def test_fault_free_matches_oracle_and_unprotected_path(pkg, O, log_n, bits, m, 
     assert np.array_equal(sums[:, 0], sums[:, 1])
 
 
+@pytest.mark.parametrize("log_n,bits,m,K", [(12, 60, 16, 9), (13, 50, 3, 5), (12, 60, 7, 50), (12, 60, 1, 17), (14, 60, 16, 48)])
+def test_tcgen05_contraction_carries_the_sums(pkg, O, log_n, bits, m, K):
+    """N >= 4096: the checksum-carrying flavour of the tcgen05 contraction (k_bconv_contract_tc5<true>), incl. ragged chunks (K not a
+    multiple of 16), more than 48 targets (second launch: input sums taken once) and a single source limb."""
+    N, moduli, bc = _plan(pkg, log_n, bits, m, K)
+    x = O.uniform_limbs(moduli[:m], N, seed=log_n + m + K)
+    out, verdict, sums = bc.modup_protected_host(x)
+    w_out, w_verdict, w_sums = O.bconv_hps_protected(x, moduli[:m], moduli[m:])
+    assert np.array_equal(out, w_out) and np.array_equal(out, bc.modup_host(x))
+    assert not verdict.any() and np.array_equal(sums, w_sums)
+    # faults: a contraction output in the first and in the last target, a y word in memory, a scale product
+    inject = [(2, 0, 5, 1 << 11), (2, K - 1, N - 1, 1 << 58), (3, m - 1, 4097 % N, 1 << 30), (1, 0, 77, 1 << 3)]
+    out, verdict, sums = bc.modup_protected_host(x, inject=inject)
+    w_out, w_verdict, w_sums = O.bconv_hps_protected(x, moduli[:m], moduli[m:], inject=inject)
+    assert np.array_equal(out, w_out) and np.array_equal(verdict, w_verdict) and np.array_equal(sums, w_sums)
+    assert verdict[m] & 1 and verdict[m + K - 1] & 1 and verdict[m - 1] & 2 and verdict[0] & 1
+
+
 @pytest.mark.parametrize("inject", [
     [(1, 2, 17, 1 << 40)],                     # scale product of source limb 2
     [(2, 3, 100, 1)],                          # lowest bit of one contraction output of target 3
