@@ -31,7 +31,9 @@ __global__ void __launch_bounds__(256) k_ct_tensor(const u64* __restrict__ a, co
     const ulonglong2 a0 = __ldcs(reinterpret_cast<const ulonglong2*>(a) + off), a1 = __ldcs(reinterpret_cast<const ulonglong2*>(a) + poly2 + off);
     const ulonglong2 b0 = __ldcs(reinterpret_cast<const ulonglong2*>(b) + off), b1 = __ldcs(reinterpret_cast<const ulonglong2*>(b) + poly2 + off);
     // reduce128: three folds of 2^bits = delta for the pseudo-Mersenne primes and in-range operands (the usual case: 5 IMAD.WIDE
-    // instead of a 128-bit Barrett's ~17 -- this streaming kernel was multiplier-bound at 51 % of the HBM peak), Barrett otherwise
+    // instead of a 128-bit Barrett's ~17), Barrett otherwise.  Measured: 40 -> 37 us at C2's shape, i.e. the multiplier was not the
+    // bound; neither is memory-level parallelism (2 / 4 pairs per thread with all loads up front: 39 / 46 us,
+    // profiles/r3e_ct_tensor_sweep.txt) -- a 37 us kernel of 3.9 waves pays its ramp and tail
     auto mul = [&](u64 x, u64 y) { return reduce128(x * y, __umul64hi(x, y), m); };
     auto mul2 = [&](u64 x0, u64 y0, u64 x1, u64 y1) {          // x0 y0 + x1 y1 mod q with one reduction
         const u64 l0 = x0 * y0, h0 = __umul64hi(x0, y0), l1 = x1 * y1, h1 = __umul64hi(x1, y1);
