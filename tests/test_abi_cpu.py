@@ -70,6 +70,20 @@ def test_bad_arguments_are_rejected(pkg):
     assert L.b200fhe_min_primitive_root(1 << 12, 97, C.byref(psi)) < 0
 
 
+def test_simulator_entries_validate_before_touching_the_device(pkg):
+    """Argument errors of the Monte-Carlo entries are reported on any machine (they precede the device probe)."""
+    import numpy as np
+    B = pkg.binding
+    z64, z48 = np.zeros((1, 64), dtype=np.uint64), np.zeros((1, 48), dtype=np.uint64)
+    for fn, args in ((B.relia_standard_host, (769, 11, z48, z48)),                     # N not a power of two
+                     (B.relia_standard_host, (771, 11, z64, z64)),                     # modulus not prime
+                     (B.relia_standard_host, (7, 3, z64, z64)),                        # N does not divide q - 1
+                     (B.relia_four_step_host, (769, 11, np.zeros((1, 32), dtype=np.uint64), np.zeros((1, 24), dtype=np.uint64)))):   # odd log N
+        with pytest.raises(pkg.B200FHEError) as e:
+            fn(*args)
+        assert "no CUDA device" not in str(e.value)
+
+
 def test_no_cpu_fallback_without_a_device(pkg):
     import torch
     if torch.cuda.is_available():
