@@ -303,27 +303,37 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_r
     const B200Mod m = p.mods[mi];
     u64* rowp = p.data + (size_t)limb * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
+    u64 ck0 = 0, ck1 = 0;
     const ulonglong2* in = reinterpret_cast<const ulonglong2*>(rowp + cl * 16);
 #pragma unroll
     for (int e = 0; e < 8; e++) { ulonglong2 x = in[e]; v[2 * e] = x.x; v[2 * e + 1] = x.y; }
     if constexpr (PROT) {
         // every loaded word is taken mod q (the transform's contract), and it is that canonical value the checksum weighs
         const ulonglong2* om = reinterpret_cast<const ulonglong2*>(p.omega + (size_t)mi * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen + cl * 16);
+        // the weighted products on the integer-multiply pipe (4 IMAD.WIDE per word); -DB200_ABFT_INV_F64 puts them on the FP64 pipe
+        // as the forward row pass does -- measured here 34.6 % against 32.0 % overhead (profiles/r3f_inv_prot_{f64,int}.txt): at the START of
+        // a kernel the shorter instruction stream wins, at the end (forward) the two were equal
+#ifndef B200_ABFT_INV_F64
+        AbftOut acc;
+#else
         AbftOutF acc;
+#endif
 #pragma unroll
         for (int e = 0; e < 8; e++) {
             const ulonglong2 o = __ldg(om + e);
             v[2 * e] = BIG ? canon2(reduce_lazy<BIG>(v[2 * e], m), m.q) : canon3(reduce_lazy<BIG>(v[2 * e], m), m.q);
             v[2 * e + 1] = BIG ? canon2(reduce_lazy<BIG>(v[2 * e + 1], m), m.q) : canon3(reduce_lazy<BIG>(v[2 * e + 1], m), m.q);
+#ifndef B200_ABFT_INV_F64
+            acc.add(o.x, v[2 * e]);
+            acc.add(o.y, v[2 * e + 1]);
+#else
             acc.add(0, o.x, v[2 * e]);
             acc.add(1, o.y, v[2 * e + 1]);
+#endif
         }
-        u64 s0, s1;
-        acc.value(s0, s1);
-        abft_commit<5>(p.abft, p.limb0 + limb, 0, s0, s1, pslot, NP);      // contains the __syncthreads the barrier needs
-    } else {
-        __syncthreads();
+        acc.value(ck0, ck1);             // committed at the END of the kernel: the FP64 chain then overlaps the first butterfly phase
     }
+    __syncthreads();                     // barrier initialised before anyone polls it
     mbar_wait(&s.bar, 0);
     gs_phase<4, BIG, false, PROT ? 1 : 0, kGsT>(v, TwList<kRowSlice>{s.twB + tslice}, m);
     unsigned char* xrow = reinterpret_cast<unsigned char*>(s.x) + (pslot * kRowsPerCta + rl) * (kRowLen * 8);
@@ -344,6 +354,7 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_r
     gs_phase<4, BIG, false, b1, kGsT>(v, TwList<1>{s.twA + rl * 16}, m);
 #pragma unroll
     for (int e = 0; e < 16; e++) rowp[e * 16 + cl] = v[e];
+    if constexpr (PROT) abft_commit<5>(p.abft, p.limb0 + limb, 0, ck0, ck1, pslot, NP);
 }
 
 // ---------------------------------------------------------------- inverse, columns
