@@ -97,7 +97,7 @@ k_fwd_col(PassArgs p) {
         if constexpr (PROT) {
             constexpr int pl = (LC + kRowLog + 1) / 2;
             static_assert(pl <= LB + kRowLog, "the weights of a thread's elements are affine in e");
-#ifdef B200_ABFT_INT                 // the r1 form: weighted products on the integer-multiply pipe
+#if defined(B200_ABFT_INT) || defined(B200_ABFT_COL_INT)                 // the r1 form: weighted products on the integer-multiply pipe
             AbftIn acc;
 #pragma unroll
             for (int e = 0; e < RA; e++) acc.add(abft_w((u32)(e * RB + g) * kRowLen + col, pl), v[e]);
