@@ -350,7 +350,10 @@ int b200fhe_keyswitch_apply(b200fhe_keyswitch* plan, const uint64_t* d_c, const 
 /* The same switch with every base conversion checksum-carrying (the checks of b200fhe_bconv_modup_protected).
  * d_verdict [dnum + 2][n_q + n_p] (uint32): rows 0..dnum-1 = the digits' ModUp conversions (alpha source-limb entries, then
  * the targets in ascending limb order); rows dnum, dnum + 1 = the ModDown conversions of out[0], out[1] (n_p source entries,
- * then n_q targets).  All zero = every check passed.  Digits and special base of at most 16 limbs. */
+ * then n_q targets).  All zero = every check passed.  Digits and special base of at most 16 limbs.
+ * CUDA graphs: the checked conversions alternate between two counter sets per plan, chosen on the HOST at call time (a call's
+ * finalize kernel clears the set the NEXT call will use), so a captured graph must hold an even number of calls per plan; a
+ * graph with one call would reuse an uncleared set on its second replay.  The unchecked b200fhe_keyswitch_apply has no such state. */
 int b200fhe_keyswitch_apply_protected(b200fhe_keyswitch* plan, const uint64_t* d_c, const uint64_t* d_evk_q, const uint64_t* d_evk_p,
                                       uint64_t* d_out, uint32_t* d_verdict, void* stream);
 
