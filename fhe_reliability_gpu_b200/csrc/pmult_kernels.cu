@@ -30,14 +30,19 @@ __device__ __forceinline__ void acc_mad(Acc192& A, u64 x, u64 y) {
         : "+l"(A.a0), "+l"(A.a1), "+l"(A.a2)
         : "l"(lo), "l"(hi));
 }
-// (a2:a1:a0) mod q, any 192-bit value
+// (a2:a1:a0) mod q, any 192-bit value.  Short sums of in-range operands (the key-switch's inner product: dnum terms) stay below
+// 2^(2 bits + 4) and take the pseudo-Mersenne fold of reduce128 (5 IMAD.WIDE) instead of two 128-bit Barretts (~34): with 3 terms
+// per output the reduction was three quarters of the kernel's multiplier work.
 __device__ __forceinline__ u64 acc_reduce(const Acc192& A, const B200Mod& m) {
+    if (A.a2 == 0) return reduce128(A.a0, A.a1, m);
     const u64 r1 = barrett128(A.a1, A.a2, m);        // (a2:a1) mod q  < q
     return barrett128(A.a0, r1, m);                  // (r1:a0) < q 2^64
 }
 
-// one thread = two consecutive coefficients of one limb, all P polynomials
-template <int P>
+// one thread = two consecutive coefficients of one limb, all P polynomials.
+// TT > 0: the number of terms at compile time (the key-switch's inner product has dnum = 2..4 of them): every load of the thread is
+// issued before the first product, instead of two terms at a time.
+template <int P, int TT = 0>
 __global__ void __launch_bounds__(256) k_pmult(const __grid_constant__ PmultPtrs ptrs, int T, u64* out, const B200Mod* mods,
                                                u32 N, u32 L, u32 start_mod, int accumulate) {
     const u32 limb = blockIdx.y;
@@ -60,16 +65,33 @@ __global__ void __launch_bounds__(256) k_pmult(const __grid_constant__ PmultPtrs
             acc[p][1].a0 = o.y;
         }
     }
+    if constexpr (TT > 0) {
+        ulonglong2 w[TT], c[TT][P];
+#pragma unroll
+        for (int k = 0; k < TT; k++) {
+            w[k] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.pt[k]) + off);
+#pragma unroll
+            for (int p = 0; p < P; p++) c[k][p] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.ct[k]) + p * poly2 + off);
+        }
+#pragma unroll
+        for (int k = 0; k < TT; k++)
+#pragma unroll
+            for (int p = 0; p < P; p++) {
+                acc_mad(acc[p][0], c[k][p].x, w[k].x);
+                acc_mad(acc[p][1], c[k][p].y, w[k].y);
+            }
+    } else {
 #pragma unroll 2
-    for (int k = 0; k < T; k++) {
-        const ulonglong2 w = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.pt[k]) + off);
-        ulonglong2 c[P];
+        for (int k = 0; k < T; k++) {
+            const ulonglong2 w = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.pt[k]) + off);
+            ulonglong2 c[P];
 #pragma unroll
-        for (int p = 0; p < P; p++) c[p] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.ct[k]) + p * poly2 + off);
+            for (int p = 0; p < P; p++) c[p] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.ct[k]) + p * poly2 + off);
 #pragma unroll
-        for (int p = 0; p < P; p++) {
-            acc_mad(acc[p][0], c[p].x, w.x);
-            acc_mad(acc[p][1], c[p].y, w.y);
+            for (int p = 0; p < P; p++) {
+                acc_mad(acc[p][0], c[p].x, w.x);
+                acc_mad(acc[p][1], c[p].y, w.y);
+            }
         }
     }
 #pragma unroll
@@ -93,8 +115,24 @@ int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out,
                 ptrs.ct[k] = k < tc ? ct[k0 + k] + poff : nullptr;
                 ptrs.pt[k] = k < tc ? pt[k0 + k] : nullptr;
             }
-            if (pc == 2) k_pmult<2><<<grid, threads, 0, s>>>(ptrs, tc, out + poff, mods, N, L, start_mod, accumulate || k0 != 0);
-            else k_pmult<1><<<grid, threads, 0, s>>>(ptrs, tc, out + poff, mods, N, L, start_mod, accumulate || k0 != 0);
+            const int acc_in = accumulate || k0 != 0;
+#define B200_PMULT_LAUNCH(PP, TTT) k_pmult<PP, TTT><<<grid, threads, 0, s>>>(ptrs, tc, out + poff, mods, N, L, start_mod, acc_in)
+            if (pc == 2) {
+                switch (tc) {
+                    case 2: B200_PMULT_LAUNCH(2, 2); break;
+                    case 3: B200_PMULT_LAUNCH(2, 3); break;
+                    case 4: B200_PMULT_LAUNCH(2, 4); break;
+                    default: B200_PMULT_LAUNCH(2, 0);
+                }
+            } else {
+                switch (tc) {
+                    case 2: B200_PMULT_LAUNCH(1, 2); break;
+                    case 3: B200_PMULT_LAUNCH(1, 3); break;
+                    case 4: B200_PMULT_LAUNCH(1, 4); break;
+                    default: B200_PMULT_LAUNCH(1, 0);
+                }
+            }
+#undef B200_PMULT_LAUNCH
             if (launches) ++*launches;
             if (T == 0) break;
         }
