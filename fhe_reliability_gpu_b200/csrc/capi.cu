@@ -319,6 +319,38 @@ extern "C" int b200fhe_nwt_backward(b200fhe_ctx* c, uint64_t* d, size_t n_poly, 
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream) {
     return run_ntt(c, true, d, n_poly, L, start, 3, (cudaStream_t)stream, d_mods_alt);
 }
+// Forward transform of n scattered limbs in ONE launch pair: entry y = data limb h_map[y].x (offset in limbs from d) with modulus
+// h_map[y].y; d_map is the same list on the device.  Returns 1 (not an error) when this size has no scatter form (log_n <= 11):
+// the caller falls back to range launches.  Used by the key-switch for the converted limbs of all digits (keyswitch.cu).
+int b200_nwt_forward_map(b200fhe_ctx* c, uint64_t* d, const uint2* d_map, const uint2* h_map, size_t n, void* stream) {
+    if (!c || !d || !d_map || !h_map) return b200_set_err(B200FHE_EINVAL, "nwt_map: null argument");
+    if (n == 0) return 0;
+    if (c->log_n <= 11 || n > 65535) return 1;
+    bool all_big = true, all_near = true;
+    for (size_t i = 0; i < n; i++) {
+        const size_t mi = h_map[i].y;
+        if (mi >= (size_t)c->L || !c->moduli[mi]) return b200_set_err(B200FHE_EINVAL, "nwt_map: modulus %zu not set", mi);
+        all_big = all_big && c->h_mods[mi].big;
+        all_near = all_near && c->h_mods[mi].near;
+    }
+    static const bool no_near = getenv("B200FHE_NO_NEAR") != nullptr;
+    const int big = (all_near && !no_near) ? 2 : all_big ? 1 : 0;
+    CK(cudaSetDevice(c->device));
+    PassArgs a;
+    a.mods = c->d_mods;
+    a.tw = c->d_tw;
+    a.rtw = c->d_rtw;
+    a.N = (u32)c->N;
+    a.L = (u32)n;
+    a.start_mod = 0;
+    a.map = d_map;
+    a.data = (u64*)d;
+    const int rc = launch_ntt(false, big, a, c->log_n, (u32)n, 3, (cudaStream_t)stream);
+    if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt_map: log_n=%d unsupported (rc=%d)", c->log_n, rc);
+    g_launches += 2;
+    CK(cudaGetLastError());
+    return 0;
+}
 // measurement hook: one pass (1 = first kernel, 2 = second kernel) of the transform
 extern "C" int b200fhe_debug_nwt_pass(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, int inverse,
                                       int pass, void* stream) {

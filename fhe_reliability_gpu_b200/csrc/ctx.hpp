@@ -32,6 +32,9 @@ struct PassArgs {
     u32 start_mod;
     u32 n_poly = 1;           // polynomials in this launch (grid.x = tiles * n_poly)
     u32 poly0 = 0;            // row passes: first polynomial of this launch (an odd last polynomial of a batch runs the one-poly form)
+    // optional scatter list (n_poly = 1): entry y of the launch transforms data limb map[y].x with modulus map[y].y -- limbs
+    // that are neither contiguous nor in modulus order (the converted limbs of every key-switch digit) in ONE launch
+    const uint2* map = nullptr;
     // protected (ABFT) forward transform only
     const u64* omega = nullptr;     // [ctx.L][N] output weights, 30-bit halves packed (lo | hi << 32)
     u64* abft = nullptr;            // [n_limbs of the call][2][4] digit-sum counters

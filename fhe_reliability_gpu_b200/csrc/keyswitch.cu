@@ -22,11 +22,13 @@
 #include "numth.hpp"
 #include <vector>
 
+#include <cstdlib>
 using namespace b200;
 
 int b200_set_err(int code, const char* fmt, ...);
 void b200_count_launches(unsigned n);
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream);
+int b200_nwt_forward_map(b200fhe_ctx* c, uint64_t* d, const uint2* d_map, const uint2* h_map, size_t n, void* stream);
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -48,6 +50,11 @@ struct b200fhe_keyswitch {
     b200fhe_bconv* down = nullptr;       // P -> Q
     ulonglong2* d_pinv = nullptr;        // [n_q] (P^-1 mod q_l, Shoup quotient)
     B200Mod* d_mods_scaled = nullptr;    // [n_q + n_p] the context's constants with N^-1 replaced by N^-1 * (conversion scale of the limb)
+    // ModUp's converted limbs of ALL digits as one scatter list for the forward NTT ((d total + g, g) for every g outside digit d):
+    // one launch pair of dnum (total - alpha) limbs instead of up to two short launches per digit (wave quantisation: 16- and
+    // 32-limb launches fill 0.9 / 1.7 waves of the column pass)
+    std::vector<uint2> up_map;
+    uint2* d_up_map = nullptr;
     uint64_t* d_ws = nullptr;                 // workspace, see offsets
     size_t o_x = 0, o_y = 0, o_up = 0, o_accq = 0, o_accp = 0, o_conv = 0, ws_words = 0;
     // fault injection armed for the next protected apply (b200fhe_keyswitch_set_inject)
@@ -86,6 +93,7 @@ extern "C" int b200fhe_keyswitch_destroy(b200fhe_keyswitch* k) {
     b200fhe_bconv_destroy(k->down);
     if (k->d_pinv) cudaFree(k->d_pinv);
     if (k->d_mods_scaled) cudaFree(k->d_mods_scaled);
+    if (k->d_up_map) cudaFree(k->d_up_map);
     if (k->d_ws) cudaFree(k->d_ws);
     delete k;
     return 0;
@@ -174,6 +182,14 @@ extern "C" int b200fhe_keyswitch_create_bgv(b200fhe_ctx* c, int n_q, int n_p, in
     if (e == cudaSuccess) e = cudaMalloc(&k->d_mods_scaled, sizeof(B200Mod) * total);
     if (e == cudaSuccess) e = cudaMemcpy(k->d_mods_scaled, ms.data(), sizeof(B200Mod) * total, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(k->d_pinv, pinv.data(), sizeof(ulonglong2) * n_q, cudaMemcpyHostToDevice);
+    if (dnum) {
+        const int alpha = n_q / dnum;
+        for (int d = 0; d < dnum; d++)
+            for (int g = 0; g < total; g++)
+                if (g < d * alpha || g >= (d + 1) * alpha) k->up_map.push_back(make_uint2((unsigned)(d * total + g), (unsigned)g));
+        if (e == cudaSuccess) e = cudaMalloc(&k->d_up_map, sizeof(uint2) * k->up_map.size());
+        if (e == cudaSuccess) e = cudaMemcpy(k->d_up_map, k->up_map.data(), sizeof(uint2) * k->up_map.size(), cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) {
         b200fhe_keyswitch_destroy(k);
         return b200_set_err(e == cudaErrorMemoryAllocation ? B200FHE_ENOMEM : B200FHE_ECUDA, "keyswitch_create: %s", cudaGetErrorString(e));
@@ -209,6 +225,10 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
     if (verdict && vntt) { RC(b200fhe_nwt_backward_protected(c, x, 1, (size_t)k->n_q, 0, vntt, nullptr, stream)); vntt += k->n_q; }
     else if (verdict) RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
     else RC(b200_nwt_backward_mods(c, x, 1, (size_t)k->n_q, 0, k->d_mods_scaled, stream));
+    // the forward transforms of all digits' converted limbs go out as one scatter launch (not for the checked transforms, whose
+    // verdicts are per range, nor for the one-kernel sizes)
+    static const bool no_merge = getenv("B200FHE_KS_NO_MERGE") != nullptr;
+    const bool merged = !vntt && !no_merge && c->log_n >= 12 && k->up_map.size() <= 65535 && k->d_up_map;
     for (int d = 0; d < k->dnum; d++) {
         b200fhe_bconv* p = k->up[d];
         const uint64_t* xd = x + (size_t)d * a * N;
@@ -227,10 +247,15 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
             if (below) RC(b200fhe_nwt_forward_protected(c, upd, 1, below, 0, vntt, nullptr, nullptr, 0, stream));
             RC(b200fhe_nwt_forward_protected(c, upd + (below + a) * N, 1, above, below + a, vntt + below, nullptr, nullptr, 0, stream));
             vntt += below + above;
-        } else {
+        } else if (!merged) {
             if (below) RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
             RC(b200fhe_nwt_forward(c, upd + (below + a) * N, 1, above, below + a, stream));
         }
+    }
+    if (merged) {
+        const int rc = b200_nwt_forward_map(c, d_up, k->d_up_map, k->up_map.data(), k->up_map.size(), stream);
+        if (rc < 0) return rc;
+        if (rc > 0) return b200_set_err(B200FHE_EUNSUPPORTED, "keyswitch_modup: scatter transform unavailable");
     }
     return 0;
 }

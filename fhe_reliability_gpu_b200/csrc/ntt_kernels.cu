@@ -68,7 +68,8 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 // resident CTAs per SM the column kernels are compiled for (register cap): 3 x 256 threads (85 registers); a cap of 4 (64
 // registers) spills and measured no faster; 512-row columns (LC = 9) fit 2
 __host__ __device__ constexpr int col_min_ctas(int LC, bool inverse) { return LC >= 9 ? 2 : 3; }
-template <int LC, int LA, int BIG, bool PROT, bool INJ>
+// MAP: the launch's entries come from the scatter list p.map (data limb, modulus) instead of (poly L + y, start_mod + y)
+template <int LC, int LA, int BIG, bool PROT, bool INJ, bool MAP = false>
 __global__ void __launch_bounds__(kTile * col_groups(LC, LA), INJ ? 1 : col_min_ctas(LC, false))
 k_fwd_col(PassArgs p) {
     constexpr int LB = LC - LA, RA = 1 << LA, RB = 1 << LB, NG = col_groups(LC, LA);
@@ -77,10 +78,12 @@ k_fwd_col(PassArgs p) {
     // grid: x = (tile, poly) with poly fastest, y = limb of the polynomial.  CTAs that share a modulus (and so a
     // twiddle tile) are dispatched back to back: the tile is read from HBM once and hit in L2 by the other polys.
     const u32 poly = blockIdx.x % p.n_poly, tile = blockIdx.x / p.n_poly;
-    const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
+    const u32 limb = poly * p.L + blockIdx.y;
+    u32 mi = p.start_mod + blockIdx.y, dl = limb;
+    if constexpr (MAP) { const uint2 e = p.map[blockIdx.y]; dl = e.x; mi = e.y; }
     const B200Mod m = p.mods[mi];
     const ulonglong2* tw = p.tw + (size_t)mi * p.N;
-    u64* base = p.data + (size_t)limb * p.N + tile * kTile;
+    u64* base = p.data + (size_t)dl * p.N + tile * kTile;
     const int c = threadIdx.x & 15, g = threadIdx.x >> 4;
     const u32 col = tile * kTile + c;
     u64 ck0 = 0, ck1 = 0;
@@ -175,7 +178,7 @@ template <int NP> constexpr int row_ctas_per_sm() {
     return (220 * 1024) / (int)sizeof(RowSmem<NP>) > 16 / NP ? 16 / NP : (220 * 1024) / (int)sizeof(RowSmem<NP>);
 }
 
-template <int BIG, bool PROT, bool INJ, int NP>
+template <int BIG, bool PROT, bool INJ, int NP, bool MAP = false>
 __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
     RowSmem<NP>& s = *reinterpret_cast<RowSmem<NP>*>(smraw);
@@ -184,7 +187,9 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_r
     const u32 ng = p.n_poly / NP, grp = blockIdx.x % ng, tile = blockIdx.x / ng;
     const int tslice = threadIdx.x % kRowSlice, pslot = threadIdx.x / kRowSlice;
     const u32 poly = p.poly0 + grp * NP + pslot;
-    const u32 limb = poly * p.L + blockIdx.y, mi = p.start_mod + blockIdx.y;
+    const u32 limb = poly * p.L + blockIdx.y;
+    u32 mi = p.start_mod + blockIdx.y, dl = limb;
+    if constexpr (MAP) { const uint2 e = p.map[blockIdx.y]; dl = e.x; mi = e.y; }
     const int cl = tslice & 15, rl = tslice >> 4;
 #ifndef B200_ABL_NOTMA
     if (threadIdx.x == 0) {
@@ -194,7 +199,7 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_r
     }
 #endif
     const B200Mod m = p.mods[mi];
-    u64* rowp = p.data + (size_t)limb * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen;
+    u64* rowp = p.data + (size_t)dl * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
 #pragma unroll
 #ifdef B200_ABL_NOLOAD
@@ -566,6 +571,22 @@ static int launch_fwd2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t
     a.n_poly = np;
     dim3 gc((kRowLen / kTile) * np, a.L);
     constexpr size_t smem = (LB > 0 ? sizeof(u64) * (kTile << LC) : 0) + sizeof(ulonglong2) * (1 << LC);
+    if constexpr (!PROT && !INJ) {
+        if (a.map) {                        // scatter list: one polynomial of a.L entries, plain transform only
+            if (np != 1) return -5;
+            if (mask & 1) {
+                if (set_smem_once<k_fwd_col<LC, LA, BIG, false, false, true>>(smem) != cudaSuccess) return -4;
+                k_fwd_col<LC, LA, BIG, false, false, true><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
+            }
+            if (mask & 2) {
+                if (set_smem_once<k_fwd_row<BIG, false, false, 1, true>>(sizeof(RowSmem<1>)) != cudaSuccess) return -4;
+                a.n_poly = 1; a.poly0 = 0;
+                k_fwd_row<BIG, false, false, 1, true><<<dim3((a.N >> kRowLog) / kRowsPerCta, a.L), kRowSlice, sizeof(RowSmem<1>), s>>>(a);
+            }
+            return 0;
+        }
+    }
+    if (a.map) return -5;
     if (mask & 1) {
         if (set_smem_once<k_fwd_col<LC, LA, BIG, PROT, INJ>>(smem) != cudaSuccess) return -4;
         k_fwd_col<LC, LA, BIG, PROT, INJ><<<gc, kTile * col_groups(LC, LA), smem, s>>>(a);
@@ -577,6 +598,7 @@ template <int LC, int LA, int BIG, bool PROT = false>
 static int launch_inv2(const PassArgs& a_in, u32 n_limbs, int mask, cudaStream_t s) {
     constexpr int LB = LC - LA;
     const u32 np = n_limbs / a_in.L;
+    if (a_in.map) return -5;              // scatter lists: forward transform only
     PassArgs a = a_in;
     a.n_poly = np;
     dim3 gc((kRowLen / kTile) * np, a.L);
