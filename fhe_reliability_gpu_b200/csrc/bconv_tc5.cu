@@ -59,7 +59,7 @@ template <bool PROT>
 __global__ void __launch_bounds__(kT5Threads, 1)
 k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B200Mod* mods, const u32* dst_idx,
                      const uint4* __restrict__ btab5 /*[K][8][16] 16-byte entries*/, u32 N, u32 m, u32 k0, u32 kcount, u64* cin, u64* cout,
-                     const __grid_constant__ BconvInjList inj) {
+                     const __grid_constant__ BconvInjList inj, u32 skip_at, u32 skip_rows) {
     extern __shared__ __align__(1024) unsigned char smraw[];
     T5Smem& s = *reinterpret_cast<T5Smem*>(smraw);
     const u32 tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -160,7 +160,9 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
 #pragma unroll
         for (u32 tl = 0; tl < 4; tl++) {
             const u32 t = c * kT5Chunk + cg * 4 + tl;
-            if (t < kcount) out[(size_t)t * N + row] = res[tl];
+            // targets from skip_at on land skip_rows rows further down: the key-switch writes a digit's targets around the digit's
+            // own limbs (which sit in the middle of the raised polynomial) in one launch
+            if (t < kcount) out[(size_t)(t + (k0 + t >= skip_at ? skip_rows : 0u)) * N + row] = res[tl];
         }
     };
 
@@ -249,7 +251,7 @@ k_bconv_contract_tc5(const u64* __restrict__ y, u64* __restrict__ out, const B20
 // Returns 0 when launched; -1 when this shape is not served here (the caller falls back to the mma.sync kernel).
 template <bool PROT>
 static int launch_t5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 k0, u32 kcount,
-                     cudaStream_t st, u64* cin, u64* cout, const BconvInjList& inj) {
+                     cudaStream_t st, u64* cin, u64* cout, const BconvInjList& inj, u32 skip_at = 0xffffffffu, u32 skip_rows = 0) {
     static const bool off = getenv("B200FHE_BCONV_NO_TC5") != nullptr;
     if (off || !btab5 || m > 16 || N % kT5Rows || N < 4096) return -1;
     int dev = 0, sms = 0;
@@ -263,7 +265,7 @@ static int launch_t5(const u64* y, u64* out, const B200Mod* mods, const u32* dst
         const u32 kc = kcount - off_k < (u32)(kT5MaxChunks * kT5Chunk) ? kcount - off_k : (u32)(kT5MaxChunks * kT5Chunk);
         const u32 grid = n_tiles < (u32)sms ? n_tiles : (u32)sms;
         k_bconv_contract_tc5<PROT><<<grid, kT5Threads, sizeof(T5Smem) + 1024, st>>>(y, out + (size_t)off_k * N, mods, dst_idx, btab5, N, m, k0 + off_k,
-                                                                                      kc, off_k ? nullptr : cin, cout, inj);
+                                                                                      kc, off_k ? nullptr : cin, cout, inj, skip_at, skip_rows);
     }
     return 0;
 }
@@ -273,6 +275,14 @@ int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const
     BconvInjList none;
     none.n = 0;
     return launch_t5<false>(y, out, mods, dst_idx, btab5, N, m, k0, kcount, st, nullptr, nullptr, none);
+}
+
+// every target of the plan in one pass, targets >= skip_at written skip_rows rows further down
+int launch_bconv_contract_tc5_skip(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
+                                   u32 skip_at, u32 skip_rows, cudaStream_t st) {
+    BconvInjList none;
+    none.n = 0;
+    return launch_t5<false>(y, out, mods, dst_idx, btab5, N, m, 0, K, st, nullptr, nullptr, none, skip_at, skip_rows);
 }
 
 int launch_bconv_contract_tc5_prot(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,

@@ -911,6 +911,21 @@ extern "C" int b200fhe_bconv_contract(b200fhe_bconv* p, const uint64_t* d_y, uin
     return 0;
 }
 
+// All K targets of the plan in one launch, written around a gap: target t lands in row t of d_out for t < skip_at and in row
+// t + skip_rows from there on (the key-switch's raised polynomial keeps the digit's own limbs in that gap).  Returns 1 when the
+// tcgen05 contraction does not serve the shape: the caller then issues the two range calls.
+int b200_bconv_contract_skip(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t skip_at, size_t skip_rows, void* stream) {
+    if (!p || !d_y || !d_out) return b200_set_err(B200FHE_EINVAL, "bconv_contract: bad arguments");
+    if (!p->d_btab5) return 1;
+    CK(cudaSetDevice(p->ctx->device));
+    if (launch_bconv_contract_tc5_skip((const u64*)d_y, (u64*)d_out, p->ctx->d_mods, p->d_dst, p->d_btab5, (u32)p->ctx->N, (u32)p->m, (u32)p->K,
+                                       (u32)skip_at, (u32)skip_rows, (cudaStream_t)stream))
+        return 1;
+    g_launches += ((size_t)p->K + 47) / 48;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int b200fhe_bconv_modup(b200fhe_bconv* p, const uint64_t* d_in, uint64_t* d_out, void* stream) {
     if (!p) return b200_set_err(B200FHE_EINVAL, "bconv_modup: null plan");
     int rc = b200fhe_bconv_scale(p, d_in, (uint64_t*)p->d_y, 0, p->m, stream);

@@ -70,6 +70,8 @@ int launch_bconv_contract_tc(const u64* y, u64* out, const B200Mod* mods, const 
 // tcgen05 / TMEM contraction (bconv_tc5.cu); returns -1 when the shape is not served there (caller falls back to launch_bconv_contract_tc)
 int launch_bconv_contract_tc5(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
                               u32 k0, u32 kcount, cudaStream_t s);
+int launch_bconv_contract_tc5_skip(const u64* y, u64* out, const B200Mod* mods, const u32* dst_idx, const uint4* btab5, u32 N, u32 m, u32 K,
+                                   u32 skip_at, u32 skip_rows, cudaStream_t s);
 struct BconvInj {          // device copy of b200fhe_bconv_inject
     u32 stage, limb;
     u64 coeff, mask;

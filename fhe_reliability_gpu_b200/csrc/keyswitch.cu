@@ -29,6 +29,7 @@ int b200_set_err(int code, const char* fmt, ...);
 void b200_count_launches(unsigned n);
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream);
 int b200_nwt_forward_map(b200fhe_ctx* c, uint64_t* d, const uint2* d_map, const uint2* h_map, size_t n, void* stream);
+int b200_bconv_contract_skip(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t skip_at, size_t skip_rows, void* stream);
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -240,8 +241,14 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
             RC(b200_bconv_modup_protected_split(p, xd, yd, upd, upd + (below + a) * N, below, verdict + (size_t)d * total, nullptr,
                                                 hit ? k->inj.data() : nullptr, hit ? k->inj.size() : 0, stream));
         } else {
-            RC(b200fhe_bconv_contract(p, xd, upd, 0, below, stream));
-            RC(b200fhe_bconv_contract(p, xd, upd + (below + a) * N, below, above, stream));
+            // one launch for the targets below and above the digit (its own limbs are the gap); two range calls where the
+            // tcgen05 contraction declines the shape
+            const int one = b200_bconv_contract_skip(p, xd, upd, below, a, stream);
+            if (one < 0) return one;
+            if (one > 0) {
+                RC(b200fhe_bconv_contract(p, xd, upd, 0, below, stream));
+                RC(b200fhe_bconv_contract(p, xd, upd + (below + a) * N, below, above, stream));
+            }
         }
         if (vntt) {
             if (below) RC(b200fhe_nwt_forward_protected(c, upd, 1, below, 0, vntt, nullptr, nullptr, 0, stream));
