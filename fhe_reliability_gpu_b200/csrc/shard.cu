@@ -28,6 +28,8 @@ using namespace b200;
 int b200_set_err(int code, const char* fmt, ...);
 void b200_count_launches(unsigned n);
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream);
+int b200_nwt_forward_map(b200fhe_ctx* c, uint64_t* d, const uint2* d_map, const uint2* h_map, size_t n, void* stream);
+int b200_bconv_contract_skip(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t skip_at, size_t skip_rows, void* stream);
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -119,6 +121,11 @@ struct b200fhe_modup_plan {
     uint64_t* d_yfull = nullptr;                   // [dnum][alpha][N] gathered digits
     cudaEvent_t ev_scaled = nullptr;
     std::vector<cudaEvent_t> ev_gathered;
+    // the converted rows of every digit as one scatter list for the forward transform ((d n_own + r, r) for the rows r outside the
+    // digit): with the limbs spread over the ranks a digit's launch is a fraction of a wave (6 limbs per digit on 8 GPUs = a third
+    // of the column pass's CTA slots), so the transforms of all digits go out together after the last contraction
+    std::vector<uint2> up_map;
+    uint2* d_up_map = nullptr;
 };
 
 // ---- pure host layout (also what the CPU tests compare with modup.ShardPlan) ----------------------------------------
@@ -236,6 +243,7 @@ extern "C" int b200fhe_modup_sharded_destroy(b200fhe_modup_plan* p) {
     if (p->d_mods_scaled) cudaFree(p->d_mods_scaled);
     if (p->d_x) cudaFree(p->d_x);
     if (p->d_yfull) cudaFree(p->d_yfull);
+    if (p->d_up_map) cudaFree(p->d_up_map);
     if (p->ev_scaled) cudaEventDestroy(p->ev_scaled);
     for (cudaEvent_t e : p->ev_gathered) cudaEventDestroy(e);
     if (p->ctx) b200fhe_ctx_destroy(p->ctx);
@@ -299,6 +307,17 @@ extern "C" int b200fhe_modup_sharded_create(b200fhe_shard* sh, int log_n, const 
     if (e == cudaSuccess) e = cudaMemcpy(p->d_mods_scaled, ms.data(), sizeof(B200Mod) * total, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_x, sizeof(uint64_t) * (p->own_q.empty() ? 1 : p->own_q.size()) * N);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_yfull, sizeof(uint64_t) * (size_t)n_q * N);
+    {
+        const size_t n_all = p->own_all.size();
+        for (int d = 0; d < dnum; d++)
+            for (size_t r = 0; r < n_all; r++)
+                if (p->conv[d] && (r < (size_t)p->below[d] || r >= (size_t)p->below[d] + (size_t)p->digit_rows[d]))
+                    p->up_map.push_back(make_uint2((unsigned)(d * n_all + r), (unsigned)r));
+        if (!p->up_map.empty()) {
+            if (e == cudaSuccess) e = cudaMalloc(&p->d_up_map, sizeof(uint2) * p->up_map.size());
+            if (e == cudaSuccess) e = cudaMemcpy(p->d_up_map, p->up_map.data(), sizeof(uint2) * p->up_map.size(), cudaMemcpyHostToDevice);
+        }
+    }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_scaled, cudaEventDisableTiming);
     p->ev_gathered.assign(dnum, nullptr);
     for (int d = 0; d < dnum && e == cudaSuccess; d++) e = cudaEventCreateWithFlags(&p->ev_gathered[d], cudaEventDisableTiming);
@@ -329,7 +348,18 @@ extern "C" int b200fhe_modup_sharded_scale(b200fhe_modup_plan* p, const uint64_t
 }
 
 // step 3 of one digit: d_y_full [alpha][N] = the digit's scaled limbs in gather (rank-major) order
-static int raise_digit(b200fhe_modup_plan* p, int d, const uint64_t* d_c_own, const uint64_t* d_y_full, uint64_t* d_up_own, void* stream) {
+static bool merged_transform(const b200fhe_modup_plan* p) {
+    static const bool no_merge = getenv("B200FHE_KS_NO_MERGE") != nullptr;
+    return !no_merge && p->d_up_map && p->ctx->log_n >= 12 && p->up_map.size() <= 65535;
+}
+static int transform_all(b200fhe_modup_plan* p, uint64_t* d_up_own, void* stream) {
+    if (!merged_transform(p)) return 0;
+    const int rc = b200_nwt_forward_map(p->ctx, d_up_own, p->d_up_map, p->up_map.data(), p->up_map.size(), stream);
+    return rc > 0 ? b200_set_err(B200FHE_EUNSUPPORTED, "modup_sharded: scatter transform unavailable") : rc;
+}
+// with_ntt = false: contraction only (the merged transform follows the last digit)
+static int raise_digit(b200fhe_modup_plan* p, int d, const uint64_t* d_c_own, const uint64_t* d_y_full, uint64_t* d_up_own, void* stream,
+                       bool with_ntt = true) {
     b200fhe_ctx* c = p->ctx;
     const size_t N = c->N, n_all = p->own_all.size();
     uint64_t* upd = d_up_own + (size_t)d * n_all * N;
@@ -338,6 +368,13 @@ static int raise_digit(b200fhe_modup_plan* p, int d, const uint64_t* d_c_own, co
         CK(cudaMemcpyAsync(upd + below * N, d_c_own + (size_t)p->digit_row0[d] * N, sizeof(uint64_t) * rows * N, cudaMemcpyDeviceToDevice,
                            (cudaStream_t)stream));
     if (!p->conv[d]) return 0;
+    if (!with_ntt) {
+        const int one = b200_bconv_contract_skip(p->conv[d], d_y_full, upd, below, rows, stream);
+        if (one <= 0) return one;
+        if (below) RC(b200fhe_bconv_contract(p->conv[d], d_y_full, upd, 0, below, stream));
+        if (above) RC(b200fhe_bconv_contract(p->conv[d], d_y_full, upd + (below + rows) * N, below, above, stream));
+        return 0;
+    }
     if (below) {
         RC(b200fhe_bconv_contract(p->conv[d], d_y_full, upd, 0, below, stream));
         RC(b200fhe_nwt_forward(c, upd, 1, below, 0, stream));
@@ -354,8 +391,9 @@ extern "C" int b200fhe_modup_sharded_raise(b200fhe_modup_plan* p, const uint64_t
                                            void* stream) {
     if (!p || !d_y_full || !d_up_own || (!p->own_q.empty() && !d_c_own)) return b200_set_err(B200FHE_EINVAL, "modup_sharded_raise: null argument");
     CK(cudaSetDevice(p->sh->device));
-    for (int d = 0; d < p->dnum; d++) RC(raise_digit(p, d, d_c_own, d_y_full[d], d_up_own, stream));
-    return 0;
+    const bool merged = merged_transform(p);
+    for (int d = 0; d < p->dnum; d++) RC(raise_digit(p, d, d_c_own, d_y_full[d], d_up_own, stream, !merged));
+    return transform_all(p, d_up_own, stream);
 }
 
 // The whole sharded ModUp of one polynomial.  d_c_own [n_own_q][N] (NTT domain, the rank's limbs of Q ascending) ->
@@ -367,9 +405,10 @@ extern "C" int b200fhe_modup_sharded(b200fhe_modup_plan* p, const uint64_t* d_c_
     cudaStream_t s = (cudaStream_t)stream;
     const size_t N = p->ctx->N, a = (size_t)p->alpha;
     RC(b200fhe_modup_sharded_scale(p, d_c_own, p->d_x, stream));
+    const bool merged = merged_transform(p);
     if (sh->world == 1) {
-        for (int d = 0; d < p->dnum; d++) RC(raise_digit(p, d, d_c_own, p->d_x + (size_t)d * a * N, d_up_own, stream));
-        return 0;
+        for (int d = 0; d < p->dnum; d++) RC(raise_digit(p, d, d_c_own, p->d_x + (size_t)d * a * N, d_up_own, stream, !merged));
+        return transform_all(p, d_up_own, stream);
     }
     NcclApi* api = nccl_api();
     if (!api || !sh->comm) return b200_set_err(B200FHE_EUNSUPPORTED, "modup_sharded: no NCCL communicator on this shard (use the scale / raise halves)");
@@ -396,7 +435,7 @@ extern "C" int b200fhe_modup_sharded(b200fhe_modup_plan* p, const uint64_t* d_c_
     }
     for (int d = 0; d < p->dnum; d++) {
         CK(cudaStreamWaitEvent(s, p->ev_gathered[d], 0));
-        RC(raise_digit(p, d, d_c_own, p->d_yfull + (size_t)d * a * N, d_up_own, stream));
+        RC(raise_digit(p, d, d_c_own, p->d_yfull + (size_t)d * a * N, d_up_own, stream, !merged));
     }
-    return 0;
+    return transform_all(p, d_up_own, stream);
 }
