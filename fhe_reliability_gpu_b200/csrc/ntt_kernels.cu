@@ -66,7 +66,8 @@ __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
 // PROT: the protected transform (config C4) -- accumulates the input side of the
 // ABFT checksum while the coefficients are loaded and honours the injection plan.
 // resident CTAs per SM the column kernels are compiled for (register cap): 3 x 256 threads (85 registers); a cap of 4 (64
-// registers) spills and measured no faster; 512-row columns (LC = 9) fit 2
+// registers) spills and measured no faster; 512-row columns (LC = 9) fit 2.  The inverse kernel at LC = 8 spills 16 bytes under the
+// cap of 3; with 2 CTAs (106 registers, no spill) it measured 111 us against 105 us per 288-limb batch: the cap of 3 stays
 __host__ __device__ constexpr int col_min_ctas(int LC, bool inverse) { return LC >= 9 ? 2 : 3; }
 // MAP: the launch's entries come from the scatter list p.map (data limb, modulus) instead of (poly L + y, start_mod + y)
 template <int LC, int LA, int BIG, bool PROT, bool INJ, bool MAP = false>
