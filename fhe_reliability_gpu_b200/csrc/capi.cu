@@ -274,7 +274,7 @@ static size_t chunk_polys(const b200fhe_ctx* c, size_t L) {
     return n ? n : 1;
 }
 static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, size_t L, size_t start, int mask,
-                   cudaStream_t s, const B200Mod* mods_alt = nullptr) {
+                   cudaStream_t s, const B200Mod* mods_alt = nullptr, const uint64_t* src = nullptr) {
     if (!c || (!d && n_poly && L)) return b200_set_err(B200FHE_EINVAL, "nwt: null argument");
     if (L == 0 || n_poly == 0) return 0;
     if (start + L > (size_t)c->L) return b200_set_err(B200FHE_EINVAL, "nwt: start_mod %zu + L %zu exceeds context (%d)", start, L, c->L);
@@ -299,6 +299,7 @@ static int run_ntt(b200fhe_ctx* c, bool inverse, uint64_t* d, size_t n_poly, siz
     for (size_t p0 = 0; p0 < n_poly; p0 += step) {
         const size_t np = n_poly - p0 < step ? n_poly - p0 : step;
         a.data = (u64*)d + p0 * L * c->N;
+        a.src = src ? (const u64*)src + p0 * L * c->N : nullptr;
         int rc = launch_ntt(inverse, big, a, c->log_n, (u32)(np * L), mask, s);
         if (rc) return b200_set_err(B200FHE_EUNSUPPORTED, "nwt: log_n=%d unsupported (rc=%d)", c->log_n, rc);
         g_launches += (c->log_n <= 11) ? 1 : ((mask == 3) ? 2 : 1);
@@ -318,6 +319,13 @@ extern "C" int b200fhe_nwt_backward(b200fhe_ctx* c, uint64_t* d, size_t n_poly, 
 // y_j = x_j (D/q_j)^-1 into the inverse NTT this way (keyswitch.cu).
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream) {
     return run_ntt(c, true, d, n_poly, L, start, 3, (cudaStream_t)stream, d_mods_alt);
+}
+// the same, out of place: d = INTT(d_src) (scaled), d_src untouched.  Sizes with the two-pass kernels only (log_n >= 12): returns 1
+// otherwise and the caller copies first.
+int b200_nwt_backward_mods_oop(b200fhe_ctx* c, const uint64_t* d_src, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt,
+                               void* stream) {
+    if (!c || c->log_n <= 11 || !d_src) return 1;
+    return run_ntt(c, true, d, n_poly, L, start, 3, (cudaStream_t)stream, d_mods_alt, d_src);
 }
 // Forward transform of n scattered limbs in ONE launch pair: entry y = data limb h_map[y].x (offset in limbs from d) with modulus
 // h_map[y].y; d_map is the same list on the device.  Returns 1 (not an error) when this size has no scatter form (log_n <= 11):

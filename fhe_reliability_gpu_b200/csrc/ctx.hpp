@@ -35,6 +35,9 @@ struct PassArgs {
     // optional scatter list (n_poly = 1): entry y of the launch transforms data limb map[y].x with modulus map[y].y -- limbs
     // that are neither contiguous nor in modulus order (the converted limbs of every key-switch digit) in ONE launch
     const uint2* map = nullptr;
+    // optional source of the inverse transform's FIRST pass (same layout as data): the rows are read from src and written to data,
+    // so a caller that must keep its input (the key-switch keeps c) needs no device copy first.  Plain transform, one polynomial per CTA.
+    const u64* src = nullptr;
     // protected (ABFT) forward transform only
     const u64* omega = nullptr;     // [ctx.L][N] output weights, 30-bit halves packed (lo | hi << 32)
     u64* abft = nullptr;            // [n_limbs of the call][2][4] digit-sum counters

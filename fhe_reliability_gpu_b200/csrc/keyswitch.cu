@@ -29,6 +29,8 @@ int b200_set_err(int code, const char* fmt, ...);
 void b200_count_launches(unsigned n);
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream);
 int b200_nwt_forward_map(b200fhe_ctx* c, uint64_t* d, const uint2* d_map, const uint2* h_map, size_t n, void* stream);
+int b200_nwt_backward_mods_oop(b200fhe_ctx* c, const uint64_t* d_src, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt,
+                               void* stream);
 int b200_bconv_contract_skip(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t skip_at, size_t skip_rows, void* stream);
 
 #define CK(call)                                                                                   \
@@ -216,7 +218,14 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
     const size_t N = c->N, a = (size_t)k->alpha, total = (size_t)k->n_q + k->n_p;
     uint64_t* x = k->d_ws + k->o_x;
     uint64_t* y = k->d_ws + k->o_y;
-    CK(cudaMemcpyAsync(x, d_c, sizeof(uint64_t) * k->n_q * N, cudaMemcpyDeviceToDevice, s));
+    // x = INTT(c): out of place where the kernels allow it (plain switch, two-pass sizes), else a device copy and the in-place form
+    bool x_done = false;
+    if (!verdict) {
+        const int rc = b200_nwt_backward_mods_oop(c, d_c, x, 1, (size_t)k->n_q, 0, k->d_mods_scaled, stream);
+        if (rc < 0) return rc;
+        x_done = rc == 0;
+    }
+    if (!x_done) CK(cudaMemcpyAsync(x, d_c, sizeof(uint64_t) * k->n_q * N, cudaMemcpyDeviceToDevice, s));
     // the digit's own limbs pass through
     for (int d = 0; d < k->dnum; d++)
         CK(cudaMemcpyAsync(d_up + ((size_t)d * total + (size_t)d * a) * N, d_c + (size_t)d * a * N, sizeof(uint64_t) * a * N,
@@ -225,7 +234,7 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
     // protected: plain inverse NTT, the scale step runs as its own checked kernel
     if (verdict && vntt) { RC(b200fhe_nwt_backward_protected(c, x, 1, (size_t)k->n_q, 0, vntt, nullptr, stream)); vntt += k->n_q; }
     else if (verdict) RC(b200fhe_nwt_backward(c, x, 1, (size_t)k->n_q, 0, stream));
-    else RC(b200_nwt_backward_mods(c, x, 1, (size_t)k->n_q, 0, k->d_mods_scaled, stream));
+    else if (!x_done) RC(b200_nwt_backward_mods(c, x, 1, (size_t)k->n_q, 0, k->d_mods_scaled, stream));
     // the forward transforms of all digits' converted limbs go out as one scatter launch (not for the checked transforms, whose
     // verdicts are per range, nor for the one-kernel sizes)
     static const bool no_merge = getenv("B200FHE_KS_NO_MERGE") != nullptr;

@@ -291,7 +291,8 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_fwd_r
 // PROT: the protected inverse transform -- the identity of the forward one read backwards: the inputs here are the
 // evaluations (SEAL order), so this pass accumulates sum_k omega_k a^_k on the words it loads (dense weights: FP64 pipe),
 // and the column pass accumulates sum_i w_i a_i on the coefficients it stores.
-template <int BIG, int NP, bool PROT>
+// OOP: out of place -- this (first) pass reads its rows from p.src instead of p.data
+template <int BIG, int NP, bool PROT, bool OOP = false>
 __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_row(PassArgs p) {
     extern __shared__ __align__(128) unsigned char smraw[];
     RowSmem<NP>& s = *reinterpret_cast<RowSmem<NP>*>(smraw);
@@ -310,7 +311,7 @@ __global__ void __launch_bounds__(kRowSlice * NP, row_ctas_per_sm<NP>()) k_inv_r
     u64* rowp = p.data + (size_t)limb * p.N + (size_t)(tile * kRowsPerCta + rl) * kRowLen;
     u64 v[16];
     u64 ck0 = 0, ck1 = 0;
-    const ulonglong2* in = reinterpret_cast<const ulonglong2*>(rowp + cl * 16);
+    const ulonglong2* in = reinterpret_cast<const ulonglong2*>((OOP ? p.src + (rowp - p.data) : rowp) + cl * 16);
 #pragma unroll
     for (int e = 0; e < 8; e++) { ulonglong2 x = in[e]; v[2 * e] = x.x; v[2 * e + 1] = x.y; }
     if constexpr (PROT) {
@@ -552,6 +553,15 @@ static int launch_fwd_row(PassArgs a, u32 np, cudaStream_t s) {
 template <int BIG, bool PROT = false>
 static int launch_inv_row(PassArgs a, u32 np, cudaStream_t s) {
     const u32 tiles = (a.N >> kRowLog) / kRowsPerCta, pairs = g_row_pairs ? np / 2 : 0;
+    if (a.src) {
+        if constexpr (!PROT) {
+            if (set_smem_once<k_inv_row<BIG, 1, false, true>>(sizeof(RowSmem<1>)) != cudaSuccess) return -4;
+            a.n_poly = np; a.poly0 = 0;
+            k_inv_row<BIG, 1, false, true><<<dim3(tiles * np, a.L), kRowSlice, sizeof(RowSmem<1>), s>>>(a);
+            return 0;
+        }
+        return -5;
+    }
     if (pairs) {
         if (set_smem_once<k_inv_row<BIG, 2, PROT>>(sizeof(RowSmem<2>)) != cudaSuccess) return -4;
         a.n_poly = pairs * 2; a.poly0 = 0;

@@ -29,6 +29,8 @@ int b200_set_err(int code, const char* fmt, ...);
 void b200_count_launches(unsigned n);
 int b200_nwt_backward_mods(b200fhe_ctx* c, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt, void* stream);
 int b200_nwt_forward_map(b200fhe_ctx* c, uint64_t* d, const uint2* d_map, const uint2* h_map, size_t n, void* stream);
+int b200_nwt_backward_mods_oop(b200fhe_ctx* c, const uint64_t* d_src, uint64_t* d, size_t n_poly, size_t L, size_t start, const B200Mod* d_mods_alt,
+                               void* stream);
 int b200_bconv_contract_skip(b200fhe_bconv* p, const uint64_t* d_y, uint64_t* d_out, size_t skip_at, size_t skip_rows, void* stream);
 
 #define CK(call)                                                                                   \
@@ -343,7 +345,12 @@ extern "C" int b200fhe_modup_sharded_scale(b200fhe_modup_plan* p, const uint64_t
     if (p->own_q.empty()) return 0;
     CK(cudaSetDevice(p->sh->device));
     const size_t N = p->ctx->N, n = p->own_q.size();
-    if (d_y_own != d_c_own) CK(cudaMemcpyAsync(d_y_own, d_c_own, sizeof(uint64_t) * n * N, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    if (d_y_own != d_c_own) {
+        // out of place where the two-pass kernels serve the size (no device copy of the owned limbs first)
+        const int rc = b200_nwt_backward_mods_oop(p->ctx, d_c_own, d_y_own, 1, n, 0, p->d_mods_scaled, stream);
+        if (rc <= 0) return rc;
+        CK(cudaMemcpyAsync(d_y_own, d_c_own, sizeof(uint64_t) * n * N, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    }
     return b200_nwt_backward_mods(p->ctx, d_y_own, 1, n, 0, p->d_mods_scaled, stream);
 }
 
