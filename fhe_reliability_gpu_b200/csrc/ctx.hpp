@@ -57,6 +57,8 @@ int launch_ntt_protected_inverse(int big, const PassArgs& a, int logn, u32 n_lim
 void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_mod, u32 n_limbs, u32* verdict, u64* sums, cudaStream_t s);
 
 // ct[k] -> [P][L][N], pt[k] -> [L][N] (host arrays of T device pointers), out [P][L][N]
+int launch_pmult_moddown(const u64* const* ct, const u64* const* pt, size_t T, const u64* conv, u64* out, const B200Mod* mods,
+                         const ulonglong2* pinv, u32 N, u32 L, cudaStream_t s);
 int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
                  u32 start_mod, int accumulate, cudaStream_t s, unsigned long long* launches);
 

@@ -282,8 +282,10 @@ extern "C" int b200fhe_keyswitch_modup(b200fhe_keyswitch* k, const uint64_t* d_c
 
 // step 4 for n_poly polynomials: d_acc_q [n_poly][n_q][N], d_acc_p [n_poly][n_p][N] (overwritten), d_out [n_poly][n_q][N]
 // (may alias d_acc_q).  n_poly <= 2.
+// convert_only: stop after conv = NTT(Conv_{P->Q}(INTT(acc_p))) (left in the workspace); the caller fuses the last step elsewhere
 static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t* d_acc_p, uint64_t* d_out, size_t n_poly,
-                        uint32_t* verdict /*optional [n_poly][n_p + n_q]*/, void* stream, uint32_t* vntt = nullptr /*[n_poly n_p] then [n_poly n_q]*/) {
+                        uint32_t* verdict /*optional [n_poly][n_p + n_q]*/, void* stream, uint32_t* vntt = nullptr /*[n_poly n_p] then [n_poly n_q]*/,
+                        bool convert_only = false) {
     if (!k || !d_acc_q || !d_acc_p || !d_out) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: null argument");
     if (n_poly < 1 || n_poly > 2) return b200_set_err(B200FHE_EINVAL, "keyswitch_moddown: n_poly must be 1 or 2");
     b200fhe_ctx* c = k->ctx;
@@ -306,6 +308,7 @@ static int moddown_impl(b200fhe_keyswitch* k, const uint64_t* d_acc_q, uint64_t*
     }
     if (verdict && vntt) RC(b200fhe_nwt_forward_protected(c, conv, n_poly, nq, 0, vntt + n_poly * np, nullptr, nullptr, 0, stream));
     else RC(b200fhe_nwt_forward(c, conv, n_poly, nq, 0, stream));
+    if (convert_only) return 0;
     dim3 grid((unsigned)((N / 2 + 255) / 256), (unsigned)nq, (unsigned)n_poly);
     k_moddown_combine<<<grid, 256, 0, s>>>((const u64*)d_acc_q, (const u64*)conv, (u64*)d_out, c->d_mods, k->d_pinv, (u32)N, (u32)nq);
     b200_count_launches(1);
@@ -333,6 +336,22 @@ static int apply_impl(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t*
     RC(modup_impl(k, d_c, up, verdict, stream, vntt));
     std::vector<const uint64_t*> ct(k->dnum), pt(k->dnum);
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
+    static const bool no_fuse = getenv("B200FHE_KS_NO_FUSED_COMBINE") != nullptr;
+    if (k->dnum <= 4 && !no_fuse) {
+        // the P part first: its ModDown conversion only needs acc_p; then the Q part's inner product with ModDown's last step
+        // (subtract, times P^-1) as its epilogue, straight into d_out -- acc_q never exists in memory
+        for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_p + (size_t)d * 2 * np * N; pt[d] = up + ((size_t)d * total + nq) * N; }
+        RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accp, 2, np, nq, 0, stream));
+        RC(moddown_impl(k, accq, accp, d_out, 2, verdict ? verdict + (size_t)k->dnum * total : nullptr, stream,
+                        vntt ? vntt + modup_ntt_count(k) : nullptr, true));
+        for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
+        if (launch_pmult_moddown((const u64* const*)ct.data(), (const u64* const*)pt.data(), (size_t)k->dnum, (const u64*)(k->d_ws + k->o_conv),
+                                 (u64*)d_out, c->d_mods, k->d_pinv, (u32)N, (u32)nq, (cudaStream_t)stream))
+            return b200_set_err(B200FHE_EUNSUPPORTED, "keyswitch_apply: fused inner product unavailable");
+        b200_count_launches(1);
+        CK(cudaGetLastError());
+        return 0;
+    }
     RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accq, 2, nq, 0, 0, stream));
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_p + (size_t)d * 2 * np * N; pt[d] = up + ((size_t)d * total + nq) * N; }
     RC(b200fhe_pmult_accum(c, ct.data(), pt.data(), (size_t)k->dnum, accp, 2, np, nq, 0, stream));

@@ -99,6 +99,65 @@ __global__ void __launch_bounds__(256) k_pmult(const __grid_constant__ PmultPtrs
         reinterpret_cast<ulonglong2*>(out)[p * poly2 + off] = make_ulonglong2(acc_reduce(acc[p][0], m), acc_reduce(acc[p][1], m));
 }
 
+// The key-switch's inner product over the Q limbs fused with ModDown's last step: out[p][l][i] =
+// (sum_k ct_k[p][l][i] pt_k[l][i] - conv[p][l][i]) Pinv_l mod q_l for the two polynomials of a switch.  The accumulated product never
+// goes to memory (2 n_q limbs written and read back otherwise) and k_moddown_combine's launch disappears; the arithmetic is the
+// same sequence (reduce to [0,q), subtract the canonical conv, one Shoup product), so the output bits are those of the two-kernel form.
+template <int TT>
+__global__ void __launch_bounds__(256) k_pmult_moddown(const __grid_constant__ PmultPtrs ptrs, const u64* __restrict__ conv, u64* __restrict__ out,
+                                                       const B200Mod* mods, const ulonglong2* __restrict__ pinv, u32 N, u32 L) {
+    const u32 limb = blockIdx.y;
+    const B200Mod m = mods[limb];
+    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i2 * 2 >= N) return;
+    const size_t off = ((size_t)limb * N) / 2 + i2, poly2 = ((size_t)L * N) / 2;
+    ulonglong2 w[TT], c[TT][2], b[2];
+#pragma unroll
+    for (int k = 0; k < TT; k++) {
+        w[k] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.pt[k]) + off);
+#pragma unroll
+        for (int p = 0; p < 2; p++) c[k][p] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.ct[k]) + p * poly2 + off);
+    }
+#pragma unroll
+    for (int p = 0; p < 2; p++) b[p] = __ldcs(reinterpret_cast<const ulonglong2*>(conv) + p * poly2 + off);
+    const ulonglong2 pv = pinv[limb];
+    const u64 q = m.q, nq = 0 - q;
+#pragma unroll
+    for (int p = 0; p < 2; p++) {
+        Acc192 a0{0, 0, 0}, a1{0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < TT; k++) {
+            acc_mad(a0, c[k][p].x, w[k].x);
+            acc_mad(a1, c[k][p].y, w[k].y);
+        }
+        const u64 rx = acc_reduce(a0, m), ry = acc_reduce(a1, m);
+        const u64 dx = rx - b[p].x + (rx < b[p].x ? q : 0), dy = ry - b[p].y + (ry < b[p].y ? q : 0);
+        ulonglong2 r;
+        r.x = canon2(shoup_mul(dx, pv.x, pv.y, nq), q);
+        r.y = canon2(shoup_mul(dy, pv.x, pv.y, nq), q);
+        reinterpret_cast<ulonglong2*>(out)[p * poly2 + off] = r;
+    }
+}
+
+// ct[k] [2][L][N], pt[k] [L][N], conv [2][L][N], out [2][L][N], moduli 0..L-1; T in 1..4 (else -1: the caller keeps the two-kernel form)
+int launch_pmult_moddown(const u64* const* ct, const u64* const* pt, size_t T, const u64* conv, u64* out, const B200Mod* mods,
+                         const ulonglong2* pinv, u32 N, u32 L, cudaStream_t s) {
+    if (T < 1 || T > 4 || N < 2) return -1;
+    PmultPtrs ptrs;
+    for (int k = 0; k < kPmultTerms; k++) {
+        ptrs.ct[k] = (size_t)k < T ? ct[k] : nullptr;
+        ptrs.pt[k] = (size_t)k < T ? pt[k] : nullptr;
+    }
+    dim3 grid((N / 2 + 255) / 256, L);
+    switch (T) {
+        case 1: k_pmult_moddown<1><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
+        case 2: k_pmult_moddown<2><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
+        case 3: k_pmult_moddown<3><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
+        default: k_pmult_moddown<4><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
+    }
+    return 0;
+}
+
 // ct[k]: T device pointers to [P][L][N]; pt[k]: T device pointers to [L][N]; out [P][L][N].
 int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
                  u32 start_mod, int accumulate, cudaStream_t s, unsigned long long* launches) {
