@@ -58,7 +58,7 @@ void launch_abft_finalize(u64* counters, const B200Mod* mods, u32 L, u32 start_m
 
 // ct[k] -> [P][L][N], pt[k] -> [L][N] (host arrays of T device pointers), out [P][L][N]
 int launch_pmult_moddown(const u64* const* ct, const u64* const* pt, size_t T, const u64* conv, u64* out, const B200Mod* mods,
-                         const ulonglong2* pinv, u32 N, u32 L, cudaStream_t s);
+                         const ulonglong2* pinv, u32 N, u32 L, cudaStream_t s, const u64* c_own = nullptr, u32 alpha = 0);
 int launch_pmult(const u64* const* ct, const u64* const* pt, size_t T, u64* out, const B200Mod* mods, u32 N, u32 P, u32 L,
                  u32 start_mod, int accumulate, cudaStream_t s, unsigned long long* launches);
 

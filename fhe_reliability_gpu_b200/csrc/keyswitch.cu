@@ -209,7 +209,9 @@ int b200_bconv_modup_protected_split(b200fhe_bconv* p, const uint64_t* d_in, uin
 // alpha source-limb entries, then the targets)
 // vntt (optional, only with verdict): per-limb verdicts of the protected transforms, in launch order: INTT(c) [n_q], then per digit
 // its targets below [d alpha] and above [total - (d + 1) alpha]
-static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, uint32_t* verdict, void* stream, uint32_t* vntt = nullptr) {
+// skip_own: leave the digits' own rows of d_up unwritten (apply reads those limbs from c itself)
+static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up, uint32_t* verdict, void* stream, uint32_t* vntt = nullptr,
+                      bool skip_own = false) {
     if (!k || !d_c || !d_up) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: null argument");
     if (!k->dnum) return b200_set_err(B200FHE_EINVAL, "keyswitch_modup: this is a ModDown-only plan (dnum = 0)");
     b200fhe_ctx* c = k->ctx;
@@ -227,7 +229,7 @@ static int modup_impl(b200fhe_keyswitch* k, const uint64_t* d_c, uint64_t* d_up,
     }
     if (!x_done) CK(cudaMemcpyAsync(x, d_c, sizeof(uint64_t) * k->n_q * N, cudaMemcpyDeviceToDevice, s));
     // the digit's own limbs pass through
-    for (int d = 0; d < k->dnum; d++)
+    for (int d = 0; d < k->dnum && !skip_own; d++)
         CK(cudaMemcpyAsync(d_up + ((size_t)d * total + (size_t)d * a) * N, d_c + (size_t)d * a * N, sizeof(uint64_t) * a * N,
                            cudaMemcpyDeviceToDevice, s));
     // unprotected: the inverse NTT's final constant carries the conversion's scale step, so x already IS y = x (D/q_j)^-1;
@@ -333,11 +335,12 @@ static int apply_impl(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t*
     uint64_t* up = k->d_ws + k->o_up;
     uint64_t* accq = k->d_ws + k->o_accq;
     uint64_t* accp = k->d_ws + k->o_accp;
-    RC(modup_impl(k, d_c, up, verdict, stream, vntt));
+    static const bool no_fuse = getenv("B200FHE_KS_NO_FUSED_COMBINE") != nullptr;
+    const bool fused = k->dnum <= 4 && !no_fuse;
+    RC(modup_impl(k, d_c, up, verdict, stream, vntt, fused));
     std::vector<const uint64_t*> ct(k->dnum), pt(k->dnum);
     for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
-    static const bool no_fuse = getenv("B200FHE_KS_NO_FUSED_COMBINE") != nullptr;
-    if (k->dnum <= 4 && !no_fuse) {
+    if (fused) {
         // the P part first: its ModDown conversion only needs acc_p; then the Q part's inner product with ModDown's last step
         // (subtract, times P^-1) as its epilogue, straight into d_out -- acc_q never exists in memory
         for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_p + (size_t)d * 2 * np * N; pt[d] = up + ((size_t)d * total + nq) * N; }
@@ -346,7 +349,7 @@ static int apply_impl(b200fhe_keyswitch* k, const uint64_t* d_c, const uint64_t*
                         vntt ? vntt + modup_ntt_count(k) : nullptr, true));
         for (int d = 0; d < k->dnum; d++) { ct[d] = d_evk_q + (size_t)d * 2 * nq * N; pt[d] = up + (size_t)d * total * N; }
         if (launch_pmult_moddown((const u64* const*)ct.data(), (const u64* const*)pt.data(), (size_t)k->dnum, (const u64*)(k->d_ws + k->o_conv),
-                                 (u64*)d_out, c->d_mods, k->d_pinv, (u32)N, (u32)nq, (cudaStream_t)stream))
+                                 (u64*)d_out, c->d_mods, k->d_pinv, (u32)N, (u32)nq, (cudaStream_t)stream, (const u64*)d_c, (u32)k->alpha))
             return b200_set_err(B200FHE_EUNSUPPORTED, "keyswitch_apply: fused inner product unavailable");
         b200_count_launches(1);
         CK(cudaGetLastError());

@@ -103,9 +103,12 @@ __global__ void __launch_bounds__(256) k_pmult(const __grid_constant__ PmultPtrs
 // (sum_k ct_k[p][l][i] pt_k[l][i] - conv[p][l][i]) Pinv_l mod q_l for the two polynomials of a switch.  The accumulated product never
 // goes to memory (2 n_q limbs written and read back otherwise) and k_moddown_combine's launch disappears; the arithmetic is the
 // same sequence (reduce to [0,q), subtract the canonical conv, one Shoup product), so the output bits are those of the two-kernel form.
+// c_own / alpha (optional): term k's plaintext-side operand for the limbs of digit k (limb / alpha == k) is read from c_own [L][N]
+// instead of pt[k] -- a digit's own limbs ARE the ciphertext's, so the key-switch need not copy them into the raised digits.
 template <int TT>
 __global__ void __launch_bounds__(256) k_pmult_moddown(const __grid_constant__ PmultPtrs ptrs, const u64* __restrict__ conv, u64* __restrict__ out,
-                                                       const B200Mod* mods, const ulonglong2* __restrict__ pinv, u32 N, u32 L) {
+                                                       const B200Mod* mods, const ulonglong2* __restrict__ pinv, u32 N, u32 L,
+                                                       const u64* __restrict__ c_own, u32 alpha) {
     const u32 limb = blockIdx.y;
     const B200Mod m = mods[limb];
     const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -114,7 +117,8 @@ __global__ void __launch_bounds__(256) k_pmult_moddown(const __grid_constant__ P
     ulonglong2 w[TT], c[TT][2], b[2];
 #pragma unroll
     for (int k = 0; k < TT; k++) {
-        w[k] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.pt[k]) + off);
+        const u64* wsrc = (c_own && limb / alpha == (u32)k) ? c_own : ptrs.pt[k];
+        w[k] = __ldcs(reinterpret_cast<const ulonglong2*>(wsrc) + off);
 #pragma unroll
         for (int p = 0; p < 2; p++) c[k][p] = __ldcs(reinterpret_cast<const ulonglong2*>(ptrs.ct[k]) + p * poly2 + off);
     }
@@ -141,7 +145,8 @@ __global__ void __launch_bounds__(256) k_pmult_moddown(const __grid_constant__ P
 
 // ct[k] [2][L][N], pt[k] [L][N], conv [2][L][N], out [2][L][N], moduli 0..L-1; T in 1..4 (else -1: the caller keeps the two-kernel form)
 int launch_pmult_moddown(const u64* const* ct, const u64* const* pt, size_t T, const u64* conv, u64* out, const B200Mod* mods,
-                         const ulonglong2* pinv, u32 N, u32 L, cudaStream_t s) {
+                         const ulonglong2* pinv, u32 N, u32 L, cudaStream_t s, const u64* c_own, u32 alpha) {
+    if (c_own && !alpha) return -1;
     if (T < 1 || T > 4 || N < 2) return -1;
     PmultPtrs ptrs;
     for (int k = 0; k < kPmultTerms; k++) {
@@ -150,10 +155,10 @@ int launch_pmult_moddown(const u64* const* ct, const u64* const* pt, size_t T, c
     }
     dim3 grid((N / 2 + 255) / 256, L);
     switch (T) {
-        case 1: k_pmult_moddown<1><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
-        case 2: k_pmult_moddown<2><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
-        case 3: k_pmult_moddown<3><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
-        default: k_pmult_moddown<4><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L); break;
+        case 1: k_pmult_moddown<1><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L, c_own, alpha); break;
+        case 2: k_pmult_moddown<2><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L, c_own, alpha); break;
+        case 3: k_pmult_moddown<3><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L, c_own, alpha); break;
+        default: k_pmult_moddown<4><<<grid, 256, 0, s>>>(ptrs, conv, out, mods, pinv, N, L, c_own, alpha); break;
     }
     return 0;
 }
